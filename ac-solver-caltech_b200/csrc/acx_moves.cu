@@ -1,0 +1,326 @@
+// acx_moves.cu -- lockstep ACMove / ACEnv.step kernels for sm_100a and their C ABI.
+//
+// Data layout in HBM: the reference's own -- rows of 2*m int8, densely packed ([N, 2m]).
+// One THREAD owns one presentation.  A CTA of TR threads owns a tile of TR rows:
+//   k_rows_tma    persistent CTAs; tiles move global<->shared with 1-D bulk async copies
+//                 (cp.async.bulk, mbarrier completion) through an S-stage ring, so per-row
+//                 shared-memory reads/writes are 64-bit and conflict-free while every HBM
+//                 transaction is a full-line bulk transfer.  Rows are rewritten IN PLACE in
+//                 the stage buffer and stored back from it.
+//   k_rows_simple same row code, plain cooperative copies; used for the tail rows, unaligned
+//                 pointers and widths without a static instantiation.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/acx.h"
+#include "acx_common.h"
+#include "acx_rows.cuh"
+#include "acx_tma.cuh"
+
+namespace acx {
+
+struct StepParams {
+    const int8_t* in;  // [n, 2m]
+    int8_t* out;       // [n, 2m] (may alias in)
+    const uint8_t* actions;
+    uint8_t* lens;    // [n,2] or null
+    uint8_t* status;  // [n] or null
+    int64_t n;
+    int64_t row0;  // first row handled by this launch
+    int m;
+    int cyclical;
+    // ACEnv.step extras (ENV kernels)
+    int32_t* steps;
+    int32_t* reward;
+    float* reward_clipped;
+    uint8_t* done;
+    uint8_t* truncated;
+    const int8_t* pool;
+    const int32_t* next_idx;
+    int horizon;
+    float clip_lo, clip_hi;
+};
+
+// ac_env.py:97-111 on one row that already sits (post-move) in shared memory
+template <bool ENV>
+__device__ __forceinline__ void row_epilogue(const StepParams& p, int64_t row, uint8_t* srow, int m, int l0, int l1,
+                                             uint32_t status, int32_t steps_in) {
+    if (ENV) {
+        const int total = l0 + l1;
+        bool done = false;
+        if (total == 2) {  // is_presentation_trivial (utils.py:57-87): |letters| == {1,2}
+            int a = (int8_t)srow[0], b = (int8_t)srow[m];
+            a = a < 0 ? -a : a;
+            b = b < 0 ? -b : b;
+            done = (a == 1 && b == 2) || (a == 2 && b == 1);
+        }
+        const int32_t max_reward = p.horizon * m * 2;          // ac_env.py:76
+        const int32_t rew = done ? max_reward : -total;        // ac_env.py:100
+        const int32_t steps = steps_in + 1;                    // ac_env.py:102
+        const bool trunc = steps >= p.horizon;                 // ac_env.py:103
+        p.reward[row] = rew;
+        if (p.reward_clipped) p.reward_clipped[row] = fminf(fmaxf((float)rew, p.clip_lo), p.clip_hi);
+        p.done[row] = done ? 1 : 0;
+        p.truncated[row] = trunc ? 1 : 0;
+        int32_t steps_out = steps;
+        if (p.pool && (done || trunc)) {  // ac_env.py:113-129 via agents/training.py:351-352
+            const int8_t* src = p.pool + (int64_t)p.next_idx[row] * 2 * m;
+            int c0 = 0, c1 = 0;
+            for (int k = 0; k < m; ++k) {
+                const int8_t v0 = src[k], v1 = src[m + k];
+                srow[k] = (uint8_t)v0;
+                srow[m + k] = (uint8_t)v1;
+                c0 += v0 != 0;
+                c1 += v1 != 0;
+            }
+            l0 = c0;
+            l1 = c1;
+            steps_out = 0;
+        }
+        p.steps[row] = steps_out;
+    }
+    if (p.lens) *reinterpret_cast<uchar2*>(p.lens + 2 * row) = make_uchar2((uint8_t)l0, (uint8_t)l1);
+    if (p.status) p.status[row] = (uint8_t)status;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int W, int MS, int TR, int S, bool ENV>
+__global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t ntiles) {
+    constexpr int ROWB = 2 * MS;
+    constexpr uint32_t TILEB = (uint32_t)TR * ROWB;
+    static_assert(TILEB % 16 == 0, "bulk copies need 16-byte multiples");
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)S * TILEB);
+    const int tid = threadIdx.x;
+    const uint32_t smem0 = smem_u32(smem);
+    const uint32_t bar0 = smem_u32(bars);
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) mbar_init(bar0 + 8 * s, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const int64_t first = blockIdx.x, stride = gridDim.x;
+    const int8_t* gin = p.in + p.row0 * ROWB;
+    int8_t* gout = p.out + p.row0 * ROWB;
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const int64_t t = first + (int64_t)s * stride;
+            if (t < ntiles) {
+                mbar_expect_tx(bar0 + 8 * s, TILEB);
+                bulk_load(smem0 + s * TILEB, gin + t * TILEB, TILEB, bar0 + 8 * s);
+            }
+        }
+    }
+
+    int it = 0;
+    for (int64_t t = first; t < ntiles; t += stride, ++it) {
+        const int s = it % S;
+        const uint32_t parity = (uint32_t)(it / S) & 1u;
+        const int64_t row = p.row0 + t * TR + tid;
+        const int move = p.actions[row];
+        int32_t steps_in = 0;
+        if (ENV) steps_in = p.steps[row];
+        mbar_wait(bar0 + 8 * s, parity);
+
+        uint8_t* srow = smem + (size_t)s * TILEB + (size_t)tid * ROWB;
+        int l0, l1;
+        uint32_t status;
+        acmove_row<W, MS>(srow, srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
+        row_epilogue<ENV>(p, row, srow, MS, l0, l1, status, steps_in);
+
+        fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            bulk_store(gout + t * TILEB, smem0 + s * TILEB, TILEB);
+            bulk_commit();
+            if (it >= 1) {  // refill the stage whose store was issued one iteration ago
+                bulk_wait_read<1>();
+                const int sp = (it - 1) % S;
+                const int64_t tn = t + (int64_t)(S - 1) * stride;
+                if (tn < ntiles) {
+                    mbar_expect_tx(bar0 + 8 * sp, TILEB);
+                    bulk_load(smem0 + sp * TILEB, gin + tn * TILEB, TILEB, bar0 + 8 * sp);
+                }
+            }
+        }
+    }
+    if (tid == 0) bulk_wait_all<0>();
+}
+
+// ---------------------------------------------------------------------------------------------
+// cooperative copy of `bytes` bytes, any alignment
+__device__ __forceinline__ void coop_copy(uint8_t* dst, const uint8_t* src, int bytes, int tid, int nthreads) {
+    if ((((uintptr_t)dst | (uintptr_t)src | (uintptr_t)bytes) & 3u) == 0) {
+        const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src);
+        uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+        for (int k = tid; k < bytes / 4; k += nthreads) d4[k] = s4[k];
+    } else {
+        for (int k = tid; k < bytes; k += nthreads) dst[k] = src[k];
+    }
+}
+
+template <int W, int MS, int TR, bool ENV>
+__global__ void __launch_bounds__(TR) k_rows_simple(const StepParams p, int64_t nrows) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int m = MS ? MS : p.m;
+    const int rowb = 2 * m;
+    const int tid = threadIdx.x;
+    const int64_t r0 = (int64_t)blockIdx.x * TR;
+    const int rows = (int)min((int64_t)TR, nrows - r0);
+    const uint8_t* gin = reinterpret_cast<const uint8_t*>(p.in) + (p.row0 + r0) * rowb;
+    uint8_t* gout = reinterpret_cast<uint8_t*>(p.out) + (p.row0 + r0) * rowb;
+    coop_copy(smem, gin, rows * rowb, tid, TR);
+    __syncthreads();
+    if (tid < rows) {
+        const int64_t row = p.row0 + r0 + tid;
+        const int move = p.actions[row];
+        int32_t steps_in = 0;
+        if (ENV) steps_in = p.steps[row];
+        uint8_t* srow = smem + (size_t)tid * rowb;
+        int l0, l1;
+        uint32_t status;
+        acmove_row<W, MS>(srow, srow, m, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
+        row_epilogue<ENV>(p, row, srow, m, l0, l1, status, steps_in);
+    }
+    __syncthreads();
+    coop_copy(gout, smem, rows * rowb, tid, TR);
+}
+
+// ---------------------------------------------------------------------------------------------
+static int g_sm_count = 0;
+
+static int sm_count() {
+    if (g_sm_count == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count <= 0) g_sm_count = 148;
+    }
+    return g_sm_count;
+}
+
+template <int W, int MS, int TR, int S, bool ENV>
+static int launch_tma(const StepParams& p, int64_t ntiles, cudaStream_t st) {
+    constexpr size_t smem = (size_t)S * TR * 2 * MS + 8 * S;
+    auto kern = k_rows_tma<W, MS, TR, S, ENV>;
+    static int ctas_per_sm = 0;
+    if (ctas_per_sm == 0) {
+        ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 0;
+        ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TR, smem));
+        ctas_per_sm = occ > 0 ? occ : 1;
+    }
+    const int64_t grid = std::min<int64_t>(ntiles, (int64_t)sm_count() * ctas_per_sm);
+    kern<<<(unsigned)grid, TR, smem, st>>>(p, ntiles);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+template <int W, int MS, int TR, bool ENV>
+static int launch_simple(const StepParams& p, int64_t nrows, cudaStream_t st) {
+    const int m = MS ? MS : p.m;
+    const size_t smem = (size_t)TR * 2 * m + 16;
+    auto kern = k_rows_simple<W, MS, TR, ENV>;
+    static size_t configured = 0;
+    if (smem > configured) {
+        ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TR * 2 * 128 + 16)));
+        configured = TR * 2 * 128 + 16;
+    }
+    const int64_t grid = (nrows + TR - 1) / TR;
+    kern<<<(unsigned)grid, TR, smem, st>>>(p, nrows);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+// rows [0, n): full tiles through the bulk-copy kernel when a static instantiation exists and the
+// buffers are 16-byte aligned; everything else through the simple kernel.
+template <int W, int MS, int TR, int S, bool ENV>
+static int run_static(StepParams p, cudaStream_t st) {
+    const bool aligned = (((uintptr_t)p.in | (uintptr_t)p.out) & 15u) == 0;
+    int64_t done_rows = 0;
+    if (aligned && p.n >= TR) {
+        const int64_t ntiles = p.n / TR;
+        p.row0 = 0;
+        int rc = launch_tma<W, MS, TR, S, ENV>(p, ntiles, st);
+        if (rc) return rc;
+        done_rows = ntiles * TR;
+    }
+    if (done_rows < p.n) {
+        p.row0 = done_rows;
+        return launch_simple<W, MS, TR, ENV>(p, p.n - done_rows, st);
+    }
+    return ACX_OK;
+}
+
+template <bool ENV>
+static int run_rows(StepParams p, cudaStream_t st) {
+    if (p.n == 0) return ACX_OK;
+    p.row0 = 0;
+    switch (p.m) {
+        case 36: return run_static<2, 36, 128, 4, ENV>(p, st);
+        case 128: return run_static<4, 128, 64, 4, ENV>(p, st);
+        default: break;
+    }
+    if (p.m <= 32) return launch_simple<1, 0, 128, ENV>(p, p.n, st);
+    if (p.m <= 64) return launch_simple<2, 0, 128, ENV>(p, p.n, st);
+    return launch_simple<4, 0, 64, ENV>(p, p.n, st);
+}
+
+}  // namespace acx
+
+using namespace acx;
+
+extern "C" int acx_move_batch(const int8_t* states_in, const uint8_t* moves, int8_t* states_out, uint8_t* lens_out,
+                              uint8_t* row_status, int64_t n, int m, int cyclical, acx_stream_t stream) {
+    if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH) return acx_fail(ACX_ERR_ARG, "acx_move_batch: need n >= 0 and 1 <= m <= 128");
+    if (n > 0 && (!states_in || !moves || !states_out)) return acx_fail(ACX_ERR_ARG, "acx_move_batch: null pointer");
+    StepParams p;
+    memset(&p, 0, sizeof p);
+    p.in = states_in;
+    p.out = states_out;
+    p.actions = moves;
+    p.lens = lens_out;
+    p.status = row_status;
+    p.n = n;
+    p.m = m;
+    p.cyclical = cyclical;
+    return run_rows<false>(p, (cudaStream_t)stream);
+}
+
+extern "C" int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
+                            const int32_t* next_idx, int32_t* reward, float* reward_clipped, uint8_t* done,
+                            uint8_t* truncated, uint8_t* lens, uint8_t* row_status, int64_t n, int m, int horizon,
+                            float clip_lo, float clip_hi, acx_stream_t stream) {
+    if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH || horizon < 1)
+        return acx_fail(ACX_ERR_ARG, "acx_env_step: need n >= 0, 1 <= m <= 128, horizon >= 1");
+    if (n > 0 && (!state || !steps || !actions || !reward || !done || !truncated))
+        return acx_fail(ACX_ERR_ARG, "acx_env_step: null pointer");
+    if ((pool == nullptr) != (next_idx == nullptr)) return acx_fail(ACX_ERR_ARG, "acx_env_step: pool and next_idx go together");
+    StepParams p;
+    memset(&p, 0, sizeof p);
+    p.in = state;
+    p.out = state;
+    p.actions = actions;
+    p.lens = lens;
+    p.status = row_status;
+    p.n = n;
+    p.m = m;
+    p.cyclical = 1;
+    p.steps = steps;
+    p.reward = reward;
+    p.reward_clipped = reward_clipped;
+    p.done = done;
+    p.truncated = truncated;
+    p.pool = pool;
+    p.next_idx = next_idx;
+    p.horizon = horizon;
+    p.clip_lo = clip_lo;
+    p.clip_hi = clip_hi;
+    return run_rows<true>(p, (cudaStream_t)stream);
+}

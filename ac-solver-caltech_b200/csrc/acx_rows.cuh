@@ -1,0 +1,337 @@
+// acx_rows.cuh -- one presentation row (int8 [r_0 | r_1], 2*m bytes, staged in shared
+// memory) <-> bit planes, and the row-level ACMove built on acx_planes.cuh.
+//
+// pack:   4 letters per 32-bit word -> one nibble of each plane with ONE multiply
+//         (a multiply-gather: the wanted bit of each byte lands in bits 28..31, the
+//         cross terms land below bit 28 or above bit 31 and never collide), inserted
+//         into the plane with a funnel shift.  3 instructions per plane per word.
+// unpack: one nibble of a plane -> 4 bytes with one multiply (bit j -> byte j), and
+//         byte = n + 253*s + (s^t) (mod 256) turns the planes back into {1,2,-1,-2,0}
+//         without any per-byte branch; sums never carry between bytes (max 255).
+#pragma once
+#include "acx_planes.cuh"
+
+namespace acx {
+
+enum : uint32_t {
+    ACX_ROW_OK = 0,
+    ACX_ROW_EMPTY_RELATOR = 1,  // the reference raises AssertionError (utils.py:264-266)
+    ACX_ROW_INVALID_INPUT = 2   // not a valid presentation on input (utils.py:13-54)
+};
+
+// raw planes of one relator as read from memory
+template <int W>
+struct RawRel {
+    BV<W> B0, B1, S7;  // bit 0, bit 1 and bit 7 of every letter byte
+};
+
+// insert the top nibble of x below the bits already in plane word p
+ACX_HD uint32_t nib_push(uint32_t x, uint32_t p) { return fshl(x, p, 4); }
+
+ACX_HD void pack_word(uint32_t x, uint32_t& b0, uint32_t& b1, uint32_t& s7, uint32_t& chk) {
+    chk |= x ^ (x >> 1);
+    b0 = nib_push((x & 0x01010101u) * 0x10204080u, b0);
+    b1 = nib_push((x & 0x02020202u) * 0x08102040u, b1);
+    s7 = nib_push((x & 0x80808080u) * 0x00204081u, s7);
+}
+
+// ---- static width (MS % 4 == 0): row words come from 8-byte aligned shared memory -------
+template <int W, int MS>
+ACX_HD void pack_row_static(const uint8_t* row, RawRel<W> (&raw)[2], uint32_t& chk) {
+    constexpr int NW = MS / 4;  // words per relator
+    uint32_t w[2 * NW];
+    const uint2* p = reinterpret_cast<const uint2*>(row);
+#pragma unroll
+    for (int k = 0; k < NW; ++k) {
+        const uint2 v = p[k];
+        w[2 * k] = v.x;
+        w[2 * k + 1] = v.y;
+    }
+    chk = 0u;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        raw[h].B0 = bv_zero<W>();
+        raw[h].B1 = bv_zero<W>();
+        raw[h].S7 = bv_zero<W>();
+#pragma unroll
+        for (int k = NW - 1; k >= 0; --k)
+            pack_word(w[h * NW + k], raw[h].B0.w[k / 8], raw[h].B1.w[k / 8], raw[h].S7.w[k / 8], chk);
+    }
+}
+
+ACX_HD uint32_t spread4(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
+
+template <int W, int MS>
+ACX_HD void unpack_row_static(uint8_t* row, const Rel<W> (&r)[2]) {
+    constexpr int NW = MS / 4;
+    uint32_t w[2 * NW];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const BV<W> N = bv_mask<W>(r[h].n);
+        const BV<W> X = bv_xor<W>(r[h].S, r[h].T);
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            const int g = k / 8, sh = 4 * (k % 8);
+            const uint32_t nn = (N.w[g] >> sh) & 0xFu;
+            const uint32_t ss = (r[h].S.w[g] >> sh) & 0xFu;
+            const uint32_t xx = (X.w[g] >> sh) & 0xFu;
+            w[h * NW + k] = spread4(nn) + spread4(xx) + 253u * spread4(ss);
+        }
+    }
+    uint2* p = reinterpret_cast<uint2*>(row);
+#pragma unroll
+    for (int k = 0; k < NW; ++k) p[k] = make_uint2(w[2 * k], w[2 * k + 1]);
+}
+
+// ---- dynamic width: any 1 <= m <= 32*W, relators may start at any byte ------------------
+template <int W>
+ACX_HD void pack_rel_dynamic(const uint8_t* rel, int m, RawRel<W>& raw, uint32_t& chk) {
+    raw.B0 = bv_zero<W>();
+    raw.B1 = bv_zero<W>();
+    raw.S7 = bv_zero<W>();
+    const int nw = (m + 3) >> 2;
+    for (int k = nw - 1; k >= 0; --k) {
+        uint32_t x = 0u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int idx = 4 * k + j;
+            const uint32_t b = (idx < m) ? (uint32_t)rel[idx] : 0u;
+            x |= b << (8 * j);
+        }
+        // make room: shift every plane left by one nibble, then insert at the bottom
+#pragma unroll
+        for (int i = W - 1; i > 0; --i) {
+            raw.B0.w[i] = fshl(raw.B0.w[i - 1], raw.B0.w[i], 4);
+            raw.B1.w[i] = fshl(raw.B1.w[i - 1], raw.B1.w[i], 4);
+            raw.S7.w[i] = fshl(raw.S7.w[i - 1], raw.S7.w[i], 4);
+        }
+        pack_word(x, raw.B0.w[0], raw.B1.w[0], raw.S7.w[0], chk);
+    }
+}
+
+template <int W>
+ACX_HD void unpack_rel_dynamic(uint8_t* rel, int m, const Rel<W>& r) {
+    BV<W> N = bv_mask<W>(r.n), S = r.S, X = bv_xor<W>(r.S, r.T);
+    const int nw = (m + 3) >> 2;
+    for (int k = 0; k < nw; ++k) {
+        const uint32_t x = spread4(N.w[0] & 0xFu) + spread4(X.w[0] & 0xFu) + 253u * spread4(S.w[0] & 0xFu);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (4 * k + j < m) rel[4 * k + j] = (uint8_t)(x >> (8 * j));
+#pragma unroll
+        for (int i = 0; i < W; ++i) {
+            N.w[i] = fshr(N.w[i], (i + 1 < W) ? N.w[i + 1] : 0u, 4);
+            S.w[i] = fshr(S.w[i], (i + 1 < W) ? S.w[i + 1] : 0u, 4);
+            X.w[i] = fshr(X.w[i], (i + 1 < W) ? X.w[i + 1] : 0u, 4);
+        }
+    }
+}
+
+// ---- byte-wise slow path: literal restatement of the reference on one row ---------------
+// Taken only for rows with letters outside {0,+-1,+-2} or with a non-reduced relator.
+// `in` and `out` may be the same buffer.
+// Follows ac_moves.py:4-156 (move, junction cancel, guard), utils.py:264-266 (validity),
+// utils.py:211-232 (stack free reduction, cyclic reduction).
+__host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_t* out, int m, int move, int cyc,
+                                         int& l0, int& l1, uint32_t& status) {
+    int cnt[2];
+    bool valid = true;
+    for (int h = 0; h < 2; ++h) {
+        int c = 0;
+        for (int k = 0; k < m; ++k) {
+            const int8_t v = in[h * m + k];
+            out[h * m + k] = v;
+            c += (v != 0);
+        }
+        cnt[h] = c;
+        if (c == 0) valid = false;
+        for (int k = c; k < m; ++k)
+            if (in[h * m + k] != 0) valid = false;
+    }
+    l0 = cnt[0];
+    l1 = cnt[1];
+    if (!valid) {
+        status = ACX_ROW_INVALID_INPUT;
+        return;
+    }
+    const uint32_t d = decode_move(move);
+    const int i = d & 1, is_conj = (d >> 1) & 1, inv = (d >> 2) & 1, gy = (d >> 3) & 1;
+    int8_t* a = out + i * m;
+    const int8_t* b = in + (1 - i) * m;
+    int la = cnt[i];
+    const int lb = cnt[1 - i];
+    if (!is_conj) {
+        int acc = 0;
+        const int lim = la < lb ? la : lb;
+        while (acc < lim) {
+            // r_j^-1 is materialised as int8 (so -(-128) wraps), the comparison is done in int
+            const int bv = inv ? (int)(int8_t)(-b[lb - 1 - acc]) : (int)b[acc];
+            if ((int)a[la - 1 - acc] != -bv) break;
+            ++acc;
+        }
+        const int nn = la + lb - 2 * acc;
+        if (nn == 0) {  // utils.py:264-266 would raise; row is handed back unchanged
+            status = ACX_ROW_EMPTY_RELATOR;
+            return;
+        }
+        if (nn <= m) {
+            for (int t = 0; t < lb - acc; ++t)
+                a[la - acc + t] = inv ? (int8_t)(-b[lb - 1 - (acc + t)]) : b[acc + t];
+            for (int k = nn; k < m; ++k) a[k] = 0;
+            la = nn;
+        }
+    } else {
+        const int g = (gy ? 2 : 1) * (inv ? -1 : 1);
+        const int sc = ((int)a[0] == -g), ec = ((int)a[la - 1] == g);
+        const int nn = la + 2 - 2 * (sc + ec);
+        if (nn == 0) {
+            status = ACX_ROW_EMPTY_RELATOR;
+            return;
+        }
+        if (nn <= m) {
+            const int core = la - sc - ec;
+            int pos;
+            if (!sc) {
+                for (int k = core - 1; k >= 0; --k) a[k + 1] = a[k];
+                a[0] = (int8_t)g;
+                pos = core + 1;
+            } else {
+                for (int k = 0; k < core; ++k) a[k] = a[k + 1];
+                pos = core;
+            }
+            if (!ec) a[pos++] = (int8_t)(-g);
+            for (int k = pos; k < m; ++k) a[k] = 0;
+            la = nn;
+        }
+    }
+    int len[2];
+    for (int h = 0; h < 2; ++h) {
+        int8_t* r = out + h * m;
+        const int n0 = (h == i) ? la : cnt[h];
+        int top = 0;
+        for (int k = 0; k < n0; ++k) {  // utils.py:211-220
+            const int8_t v = r[k];
+            if (top > 0 && (int)r[top - 1] == -(int)v) --top;
+            else r[top++] = v;
+        }
+        int n = top;
+        if (cyc && n > 0) {  // utils.py:223-232
+            int k = 0;
+            while (2 * k + 1 < n && (int)r[k] == -(int)r[n - 1 - k]) ++k;
+            if (k) {
+                for (int t = 0; t < n - 2 * k; ++t) r[t] = r[t + k];
+                n -= 2 * k;
+            }
+        }
+        for (int k = n; k < n0; ++k) r[k] = 0;
+        len[h] = n;
+    }
+    l0 = len[0];
+    l1 = len[1];
+    status = ACX_ROW_OK;
+}
+
+template <int W>
+ACX_HD Rel<W> rel_select(bool second, const Rel<W>& r0, const Rel<W>& r1) {
+    Rel<W> o;
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+        o.S.w[i] = second ? r1.S.w[i] : r0.S.w[i];
+        o.T.w[i] = second ? r1.T.w[i] : r0.T.w[i];
+    }
+    o.n = second ? r1.n : r0.n;
+    return o;
+}
+
+// Result of classifying a packed row
+enum : int { ROW_FAST = 0, ROW_SLOW = 1, ROW_INVALID = 2 };
+
+template <int W>
+ACX_HD int classify_row(const RawRel<W> (&raw)[2], uint32_t chk, Rel<W> (&r)[2], int (&cnt)[2]) {
+    bool alpha_ok = (chk & 0x7C7C7C7Cu) == 0u;
+    bool valid = true, reduced = true;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const BV<W> bad3 = bv_and<W>(bv_andn<W>(raw[h].B1, raw[h].S7), raw[h].B0);  // byte 0x03
+        const BV<W> badn = bv_andn<W>(raw[h].S7, raw[h].B1);                        // 0xFC, 0xFD
+        alpha_ok = alpha_ok && !bv_any<W>(bv_or<W>(bad3, badn));
+        const BV<W> N = bv_or<W>(raw[h].B0, raw[h].B1);
+        const int n = bv_popc<W>(N);
+        cnt[h] = n;
+        valid = valid && (n > 0) && bv_eq<W>(N, bv_mask<W>(n));
+        r[h].S = raw[h].S7;
+        r[h].T = bv_andn<W>(raw[h].B1, raw[h].B0);
+        r[h].n = n;
+        reduced = reduced && !rel_has_adjacent_inverse<W>(r[h]);
+    }
+    if (!alpha_ok) return ROW_SLOW;  // the byte path also does the validity test
+    if (!valid) return ROW_INVALID;
+    return reduced ? ROW_FAST : ROW_SLOW;
+}
+
+// Apply move `move` to the planes (fast path).  Returns the row status.
+template <int W>
+ACX_HD uint32_t apply_move_planes(Rel<W> (&r)[2], int move, int m, bool cyc) {
+    const uint32_t d = decode_move(move);
+    const bool i = d & 1u, is_conj = d & 2u, inv = d & 4u;
+    const uint32_t gy = (d >> 3) & 1u;
+    Rel<W> a = rel_select<W>(i, r[0], r[1]);
+    if (!is_conj) {
+        Rel<W> b = rel_select<W>(!i, r[0], r[1]);
+        if (inv) b = rel_inverse<W>(b);
+        rel_concat<W>(a, b, m);
+    } else {
+        rel_conjugate<W>(a, inv ? 1u : 0u, gy, m);
+    }
+    if (a.n == 0) return ACX_ROW_EMPTY_RELATOR;
+    if (i) r[1] = a;
+    else r[0] = a;
+    if (cyc) {
+        rel_cyclic_reduce<W>(r[0]);
+        rel_cyclic_reduce<W>(r[1]);
+    }
+    return ACX_ROW_OK;
+}
+
+// One ACMove on one row in shared memory: in_row -> out_row (may be the same buffer: the row is
+// read completely before anything is written on the plane path).
+// MS > 0: static width (MS % 4 == 0, rows 8-byte aligned); MS == 0: dynamic width m.
+template <int W, int MS>
+ACX_HD void acmove_row(const uint8_t* in_row, uint8_t* out_row, int m_rt, int move, bool cyc,
+                                           int& l0, int& l1, uint32_t& status) {
+    const int m = MS ? MS : m_rt;
+    RawRel<W> raw[2];
+    uint32_t chk = 0u;
+    if (MS) {
+        pack_row_static<W, (MS ? MS : 4)>(in_row, raw, chk);
+    } else {
+        pack_rel_dynamic<W>(in_row, m, raw[0], chk);
+        pack_rel_dynamic<W>(in_row + m, m, raw[1], chk);
+    }
+    Rel<W> r[2];
+    int cnt[2];
+    const int cls = classify_row<W>(raw, chk, r, cnt);
+    if (cls == ROW_SLOW) {
+        slow_acmove(reinterpret_cast<const int8_t*>(in_row), reinterpret_cast<int8_t*>(out_row), m, move, cyc ? 1 : 0,
+                    l0, l1, status);
+        return;
+    }
+    status = (cls == ROW_INVALID) ? (uint32_t)ACX_ROW_INVALID_INPUT : apply_move_planes<W>(r, move, m, cyc);
+    if (status != ACX_ROW_OK) {  // row handed back unchanged, lengths = non-zero counts of the input
+        if (out_row != in_row)
+            for (int k = 0; k < 2 * m; ++k) out_row[k] = in_row[k];
+        l0 = cnt[0];
+        l1 = cnt[1];
+        return;
+    }
+    if (MS) {
+        unpack_row_static<W, (MS ? MS : 4)>(out_row, r);
+    } else {
+        unpack_rel_dynamic<W>(out_row, m, r[0]);
+        unpack_rel_dynamic<W>(out_row + m, m, r[1]);
+    }
+    l0 = r[0].n;
+    l1 = r[1].n;
+}
+
+}  // namespace acx

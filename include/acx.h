@@ -1,0 +1,78 @@
+/*
+ * include/acx.h -- C ABI of libacx.so, the sm_100a Andrews-Curtis move engine.
+ *
+ * The reference (Avi161/AC-Solver-Caltech) has no FFI: its boundary for this path is a set of
+ * Python call signatures.  Each entry point below names the reference function(s) whose work it
+ * does for a whole batch in one launch; ac-solver-caltech_b200/ac_solver/ re-exports the reference
+ * names on top of these.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller unless the name ends in `_host`;
+ *   - a presentation row is 2*m int8: [r_0 | r_1], letters 1,-1,2,-2, zero padded on the right
+ *     of each half (ac_solver/envs/utils.py:4-7);  1 <= m <= 128;
+ *   - calls are asynchronous on `stream` (a cudaStream_t passed as void*); nothing is allocated
+ *     or freed across the boundary except opaque handles;
+ *   - return value: 0 ok, < 0 error (acx_last_error() has the text, thread-local);
+ *   - per-row anomalies never fail the call: they go to row_status[] (ACX_ROW_*), and the row is
+ *     handed back unchanged.  The Python wrappers raise AssertionError for them exactly where the
+ *     reference does (utils.py:264-266).
+ *   - there is no CPU implementation behind any of these: without a CUDA device they fail.
+ */
+#ifndef ACX_H
+#define ACX_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* acx_stream_t;
+
+enum {
+    ACX_OK = 0,
+    ACX_ERR_ARG = -1,  /* bad argument (null pointer, m out of range, ...) */
+    ACX_ERR_CUDA = -2, /* a CUDA runtime call failed */
+    ACX_ERR_STATE = -3 /* handle in the wrong state */
+};
+
+enum {
+    ACX_ROW_STATUS_OK = 0,
+    ACX_ROW_STATUS_EMPTY_RELATOR = 1, /* reference raises AssertionError (utils.py:264-266) */
+    ACX_ROW_STATUS_INVALID_INPUT = 2  /* input is not a valid presentation (utils.py:13-54) */
+};
+
+#define ACX_MAX_RELATOR_LENGTH 128
+
+const char* acx_last_error(void);
+int acx_version(void);
+/* number of CUDA devices visible; < 0 on error */
+int acx_device_count(void);
+
+/* ACMove in lockstep -- ac_solver/envs/ac_moves.py:159-231 (decode :188-206, concatenate_relators
+ * :4-76, conjugate :79-156) followed by simplify_presentation, ac_solver/envs/utils.py:246-283.
+ * states_out may alias states_in.  lens_out [n,2] and row_status [n] may be NULL. */
+int acx_move_batch(const int8_t* states_in, const uint8_t* moves, int8_t* states_out, uint8_t* lens_out,
+                   uint8_t* row_status, int64_t n, int m, int cyclical, acx_stream_t stream);
+
+/* ACEnv.step in lockstep, in place -- ac_solver/envs/ac_env.py:91-111 (cyclical=True move,
+ * done = total length 2 and trivial, reward = max_reward*done - total*(1-done) with
+ * max_reward = horizon*m*2 (:76), count_steps += 1, truncated = count_steps >= horizon), fused
+ * with the reset the PPO loop applies to finished envs (ACEnv.reset, ac_env.py:113-129;
+ * agents/training.py:351-352): when pool != NULL and done|truncated, state <- pool[next_idx[e]],
+ * steps <- 0.  reward_clipped (optional) = clip(reward, clip_lo, clip_hi), the TransformReward
+ * wrapper of agents/environment.py:48-52.  lens [n,2], row_status [n] may be NULL. */
+int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
+                 const int32_t* next_idx, int32_t* reward, float* reward_clipped, uint8_t* done,
+                 uint8_t* truncated, uint8_t* lens, uint8_t* row_status, int64_t n, int m, int horizon,
+                 float clip_lo, float clip_hi, acx_stream_t stream);
+
+/* All 12 successors of every parent in one launch -- the `for action in range(12)` loops of
+ * ac_solver/search/greedy.py:76-83 and ac_solver/search/breadth_first.py:69-76.
+ * children [f,12,2m], child_lens [f,12,2], child_status [f,12] (the last two may be NULL). */
+int acx_expand12(const int8_t* parents, int8_t* children, uint8_t* child_lens, uint8_t* child_status,
+                 int64_t f, int m, int cyclical, acx_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACX_H */

@@ -1,0 +1,47 @@
+// tests/host_harness/acx_host.cu -- TEST INFRASTRUCTURE.
+// Runs the product's row arithmetic (csrc/acx_rows.cuh, __host__ __device__) on the CPU so that
+// `pytest -m "not gpu"` can compare it with the oracle before any GPU time is spent.  Nothing in
+// the product loads this library.
+#include <stdint.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../../ac-solver-caltech_b200/csrc/acx_rows.cuh"
+
+using namespace acx;
+
+template <int W, int MS>
+static void run(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status, int64_t n, int m,
+                int cyc, int inplace) {
+    const int rowb = 2 * m;
+    std::vector<uint64_t> a(rowb / 8 + 2), b(rowb / 8 + 2);  // 8-byte aligned scratch rows
+    for (int64_t r = 0; r < n; ++r) {
+        uint8_t* ia = reinterpret_cast<uint8_t*>(a.data());
+        uint8_t* ob = inplace ? ia : reinterpret_cast<uint8_t*>(b.data());
+        memcpy(ia, in + r * rowb, rowb);
+        int l0 = -1, l1 = -1;
+        uint32_t st = 99;
+        acmove_row<W, MS>(ia, ob, m, moves[r], cyc != 0, l0, l1, st);
+        memcpy(out + r * rowb, ob, rowb);
+        lens[2 * r] = (uint8_t)l0;
+        lens[2 * r + 1] = (uint8_t)l1;
+        status[r] = (uint8_t)st;
+    }
+}
+
+// variant: 0 = dynamic width, 1 = static instantiation (m must be 36 or 128)
+extern "C" int acxh_move_batch(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status,
+                               int64_t n, int m, int cyc, int variant, int inplace) {
+    if (variant == 1) {
+        if (m == 36) run<2, 36>(in, moves, out, lens, status, n, m, cyc, inplace);
+        else if (m == 128) run<4, 128>(in, moves, out, lens, status, n, m, cyc, inplace);
+        else return -1;
+        return 0;
+    }
+    if (m <= 32) run<1, 0>(in, moves, out, lens, status, n, m, cyc, inplace);
+    else if (m <= 64) run<2, 0>(in, moves, out, lens, status, n, m, cyc, inplace);
+    else if (m <= 128) run<4, 0>(in, moves, out, lens, status, n, m, cyc, inplace);
+    else return -1;
+    return 0;
+}
