@@ -1,0 +1,53 @@
+"""ctypes loader of libacx.so (built in-tree by ../build.py).
+
+There is no fallback: if the library is missing or a call fails, an exception is raised.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libacx.so")
+_lib = None
+
+c_i8p = ctypes.c_void_p  # device pointers are passed as integers
+_I64, _I32, _F32, _PTR = ctypes.c_int64, ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+
+_SIGNATURES = {
+    "acx_last_error": (ctypes.c_char_p, []),
+    "acx_version": (_I32, []),
+    "acx_device_count": (_I32, []),
+    "acx_set_device": (_I32, [_I32]),
+    "acx_move_batch": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR]),
+    "acx_env_step": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR,
+                            _I64, _I32, _I32, _F32, _F32, _PTR]),
+}
+
+
+class AcxError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python ac-solver-caltech_b200/build.py` "
+                "(there is no CPU or PyTorch fallback for the AC-move engine)")
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def exported_symbols():
+    return list(_SIGNATURES)
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().acx_last_error()
+        raise AcxError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")

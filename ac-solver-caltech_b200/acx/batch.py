@@ -1,0 +1,83 @@
+"""Batch entry points on torch CUDA tensors (thin wrappers over the C ABI in include/acx.h).
+
+Tensors are used for device memory and streams only; all arithmetic happens in libacx.so.
+"""
+import torch
+
+from . import _lib
+
+_current_dev = [None]
+
+
+def _prep(device):
+    if device.type != "cuda":
+        raise _lib.AcxError("acx needs CUDA tensors: there is no CPU implementation of the AC-move engine")
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if _current_dev[0] != idx:
+        _lib.check(_lib.lib().acx_set_device(idx), "acx_set_device")
+        _current_dev[0] = idx
+    return torch.cuda.current_stream(idx).cuda_stream
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def _chk(t, dtype, shape, name):
+    if t.dtype != dtype or not t.is_contiguous() or tuple(t.shape) != tuple(shape):
+        raise ValueError(f"{name}: expected contiguous {dtype} of shape {tuple(shape)}, got {t.dtype} {tuple(t.shape)}")
+
+
+def move_batch(states, moves, cyclical=True, out=None, want_lens=True, want_status=True):
+    """ACMove over rows: states int8 [N,2m], moves uint8 [N] -> (next, lens u8 [N,2], status u8 [N])."""
+    n, row = states.shape
+    m = row // 2
+    _chk(states, torch.int8, (n, 2 * m), "states")
+    _chk(moves, torch.uint8, (n,), "moves")
+    stream = _prep(states.device)
+    if out is None:
+        out = torch.empty_like(states)
+    else:
+        _chk(out, torch.int8, (n, 2 * m), "out")
+    lens = torch.empty((n, 2), dtype=torch.uint8, device=states.device) if want_lens else None
+    status = torch.empty((n,), dtype=torch.uint8, device=states.device) if want_status else None
+    rc = _lib.lib().acx_move_batch(_ptr(states), _ptr(moves), _ptr(out), _ptr(lens), _ptr(status), n, m,
+                                   int(bool(cyclical)), stream)
+    _lib.check(rc, "acx_move_batch")
+    return out, lens, status
+
+
+class EnvBuffers:
+    """Device-resident state of N lockstep ACEnv instances (ac_env.py:53-89 fields, as arrays)."""
+
+    def __init__(self, state, horizon, pool=None):
+        n, row = state.shape
+        self.n, self.m = n, row // 2
+        self.horizon = int(horizon)
+        dev = state.device
+        self.state = state.contiguous()
+        self.steps = torch.zeros(n, dtype=torch.int32, device=dev)
+        self.lens = torch.empty((n, 2), dtype=torch.uint8, device=dev)
+        self.reward = torch.empty(n, dtype=torch.int32, device=dev)
+        self.reward_clipped = torch.empty(n, dtype=torch.float32, device=dev)
+        self.done = torch.empty(n, dtype=torch.uint8, device=dev)
+        self.truncated = torch.empty(n, dtype=torch.uint8, device=dev)
+        self.status = torch.empty(n, dtype=torch.uint8, device=dev)
+        self.pool = None if pool is None else pool.contiguous()
+
+
+def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0)):
+    """ACEnv.step over all envs in place (ac_env.py:91-111) + reset of finished envs from buf.pool."""
+    _chk(actions, torch.uint8, (buf.n,), "actions")
+    stream = _prep(buf.state.device)
+    pool = buf.pool if next_idx is not None else None
+    if next_idx is not None:
+        _chk(next_idx, torch.int32, (buf.n,), "next_idx")
+        if pool is None:
+            raise ValueError("next_idx given but the env buffers hold no pool")
+    rc = _lib.lib().acx_env_step(_ptr(buf.state), _ptr(buf.steps), _ptr(actions), _ptr(pool), _ptr(next_idx),
+                                 _ptr(buf.reward), _ptr(buf.reward_clipped), _ptr(buf.done), _ptr(buf.truncated),
+                                 _ptr(buf.lens), _ptr(buf.status), buf.n, buf.m, buf.horizon,
+                                 float(clip[0]), float(clip[1]), stream)
+    _lib.check(rc, "acx_env_step")
+    return buf

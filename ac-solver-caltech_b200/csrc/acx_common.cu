@@ -23,3 +23,8 @@ extern "C" int acx_device_count(void) {
     if (e != cudaSuccess) return acx_fail(ACX_ERR_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
     return n;
 }
+extern "C" int acx_set_device(int dev) {
+    cudaError_t e = cudaSetDevice(dev);
+    if (e != cudaSuccess) return acx_fail(ACX_ERR_CUDA, "cudaSetDevice(%d): %s", dev, cudaGetErrorString(e));
+    return ACX_OK;
+}

@@ -5,6 +5,8 @@
 #include <algorithm>
 #include <cstdint>
 
+#define ACX_MAX_DEVICES 64
+
 int acx_fail(int code, const char* fmt, ...);
 
 #define ACX_CUDA(expr)                                                                         \

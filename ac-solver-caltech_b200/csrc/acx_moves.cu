@@ -193,30 +193,36 @@ __global__ void __launch_bounds__(TR) k_rows_simple(const StepParams p, int64_t 
 }
 
 // ---------------------------------------------------------------------------------------------
-static int g_sm_count = 0;
+static int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < ACX_MAX_DEVICES) ? dev : 0;
+}
 
 static int sm_count() {
-    if (g_sm_count == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-        if (g_sm_count <= 0) g_sm_count = 148;
+    static int cached[ACX_MAX_DEVICES] = {0};
+    const int dev = current_device();
+    if (cached[dev] == 0) {
+        int n = 0;
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        cached[dev] = n > 0 ? n : 148;
     }
-    return g_sm_count;
+    return cached[dev];
 }
 
 template <int W, int MS, int TR, int S, bool ENV>
 static int launch_tma(const StepParams& p, int64_t ntiles, cudaStream_t st) {
     constexpr size_t smem = (size_t)S * TR * 2 * MS + 8 * S;
     auto kern = k_rows_tma<W, MS, TR, S, ENV>;
-    static int ctas_per_sm = 0;
-    if (ctas_per_sm == 0) {
+    static int ctas_per_sm[ACX_MAX_DEVICES] = {0};  // function attributes are per device
+    const int dev = current_device();
+    if (ctas_per_sm[dev] == 0) {
         ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int occ = 0;
         ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TR, smem));
-        ctas_per_sm = occ > 0 ? occ : 1;
+        ctas_per_sm[dev] = occ > 0 ? occ : 1;
     }
-    const int64_t grid = std::min<int64_t>(ntiles, (int64_t)sm_count() * ctas_per_sm);
+    const int64_t grid = std::min<int64_t>(ntiles, (int64_t)sm_count() * ctas_per_sm[dev]);
     kern<<<(unsigned)grid, TR, smem, st>>>(p, ntiles);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
@@ -227,10 +233,11 @@ static int launch_simple(const StepParams& p, int64_t nrows, cudaStream_t st) {
     const int m = MS ? MS : p.m;
     const size_t smem = (size_t)TR * 2 * m + 16;
     auto kern = k_rows_simple<W, MS, TR, ENV>;
-    static size_t configured = 0;
-    if (smem > configured) {
+    static bool configured[ACX_MAX_DEVICES] = {false};
+    const int dev = current_device();
+    if (!configured[dev] && smem > 48 * 1024) {
         ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TR * 2 * 128 + 16)));
-        configured = TR * 2 * 128 + 16;
+        configured[dev] = true;
     }
     const int64_t grid = (nrows + TR - 1) / TR;
     kern<<<(unsigned)grid, TR, smem, st>>>(p, nrows);

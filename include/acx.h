@@ -47,6 +47,8 @@ const char* acx_last_error(void);
 int acx_version(void);
 /* number of CUDA devices visible; < 0 on error */
 int acx_device_count(void);
+/* make `dev` the current device of the calling thread for this library's runtime */
+int acx_set_device(int dev);
 
 /* ACMove in lockstep -- ac_solver/envs/ac_moves.py:159-231 (decode :188-206, concatenate_relators
  * :4-76, conjugate :79-156) followed by simplify_presentation, ac_solver/envs/utils.py:246-283.

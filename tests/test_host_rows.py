@@ -1,0 +1,42 @@
+"""The product's row arithmetic (bit planes + byte slow path), compiled for the host, against the
+oracle and the reference-generated golden vectors.  CPU only; the same code runs on the GPU."""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import random_rows
+from host_harness import harness
+
+
+def _variants(m):
+    return (0, 1) if m in (36, 128) else (0,)
+
+
+@pytest.mark.parametrize("m", [4, 7, 18, 36, 128])
+def test_host_rows_golden(golden_dir, m):
+    g = np.load(os.path.join(golden_dir, "moves_golden.npz"))
+    rows, mv, cyc, out, lens, raised = (g[f"{k}_{m}"] for k in ("rows", "moves", "cyc", "out", "lens", "raised"))
+    for c in (0, 1):
+        sel = cyc == c
+        for variant in _variants(m):
+            for inplace in (0, 1):
+                o, l, st = harness.move_batch(rows[sel], mv[sel], c, variant, inplace)
+                assert np.array_equal(o, out[sel])
+                ok = raised[sel] == 0
+                assert np.array_equal(l[ok].astype(np.int32), lens[sel][ok])
+                assert np.array_equal(st != 0, raised[sel] != 0)
+
+
+@pytest.mark.parametrize("m", [1, 2, 3, 5, 8, 12, 31, 32, 33, 36, 40, 63, 64, 65, 100, 127, 128])
+def test_host_rows_fuzz(oracle, m):
+    rng = np.random.default_rng(100 + m)
+    rows = random_rows(rng, 4000, m)
+    mv = rng.integers(0, 12, len(rows)).astype(np.uint8)
+    for c in (0, 1):
+        eo, el, es = oracle.acmove_batch(rows, mv, cyclical=c, threads=4)
+        for variant in _variants(m):
+            o, l, st = harness.move_batch(rows, mv, c, variant, 1)
+            assert np.array_equal(o, eo)
+            assert np.array_equal(l.astype(np.int32), el)
+            assert np.array_equal(st, es)
