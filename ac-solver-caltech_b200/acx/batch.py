@@ -47,6 +47,21 @@ def move_batch(states, moves, cyclical=True, out=None, want_lens=True, want_stat
     return out, lens, status
 
 
+def expand12(parents, cyclical=False, want_lens=True, want_status=True):
+    """All 12 successors: parents int8 [F,2m] -> (children [F,12,2m], lens u8 [F,12,2], status u8 [F,12])."""
+    f, row = parents.shape
+    m = row // 2
+    _chk(parents, torch.int8, (f, 2 * m), "parents")
+    stream = _prep(parents.device)
+    children = torch.empty((f, 12, row), dtype=torch.int8, device=parents.device)
+    lens = torch.empty((f, 12, 2), dtype=torch.uint8, device=parents.device) if want_lens else None
+    status = torch.empty((f, 12), dtype=torch.uint8, device=parents.device) if want_status else None
+    rc = _lib.lib().acx_expand12(_ptr(parents), _ptr(children), _ptr(lens), _ptr(status), f, m,
+                                 int(bool(cyclical)), stream)
+    _lib.check(rc, "acx_expand12")
+    return children, lens, status
+
+
 class EnvBuffers:
     """Device-resident state of N lockstep ACEnv instances (ac_env.py:53-89 fields, as arrays)."""
 

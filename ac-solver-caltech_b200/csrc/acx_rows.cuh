@@ -132,7 +132,7 @@ ACX_HD void unpack_rel_dynamic(uint8_t* rel, int m, const Rel<W>& r) {
 // `in` and `out` may be the same buffer.
 // Follows ac_moves.py:4-156 (move, junction cancel, guard), utils.py:264-266 (validity),
 // utils.py:211-232 (stack free reduction, cyclic reduction).
-__host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_t* out, int m, int move, int cyc,
+static __host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_t* out, int m, int move, int cyc,
                                          int& l0, int& l1, uint32_t& status) {
     int cnt[2];
     bool valid = true;
