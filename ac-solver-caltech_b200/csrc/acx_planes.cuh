@@ -23,13 +23,13 @@
 namespace acx {
 
 #ifdef __CUDA_ARCH__
-ACX_HD uint32_t fshl(uint32_t lo, uint32_t hi, int s) { return fshl(lo, hi, s); }
-ACX_HD uint32_t fshr(uint32_t lo, uint32_t hi, int s) { return fshr(lo, hi, s); }
-ACX_HD uint32_t fshl_c(uint32_t lo, uint32_t hi, int s) { return fshl_c(lo, hi, s); }
-ACX_HD uint32_t fshr_c(uint32_t lo, uint32_t hi, int s) { return fshr_c(lo, hi, s); }
-ACX_HD uint32_t brev32(uint32_t x) { return brev32(x); }
+ACX_HD uint32_t fshl(uint32_t lo, uint32_t hi, int s) { return __funnelshift_l(lo, hi, s); }
+ACX_HD uint32_t fshr(uint32_t lo, uint32_t hi, int s) { return __funnelshift_r(lo, hi, s); }
+ACX_HD uint32_t fshl_c(uint32_t lo, uint32_t hi, int s) { return __funnelshift_lc(lo, hi, s); }
+ACX_HD uint32_t fshr_c(uint32_t lo, uint32_t hi, int s) { return __funnelshift_rc(lo, hi, s); }
+ACX_HD uint32_t brev32(uint32_t x) { return __brev(x); }
 ACX_HD int clz32(uint32_t x) { return __clz(x); }
-ACX_HD int popc32(uint32_t x) { return popc32(x); }
+ACX_HD int popc32(uint32_t x) { return __popc(x); }
 #else
 ACX_HD uint32_t fshl(uint32_t lo, uint32_t hi, int s) {
     s &= 31;
