@@ -19,8 +19,7 @@ _SIGNATURES = {
     "acx_set_device": (_I32, [_I32]),
     "acx_move_batch": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR]),
     "acx_expand12": (_I32, [_PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR]),
-    "acx_env_step": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR,
-                            _I64, _I32, _I32, _F32, _F32, _PTR]),
+    "acx_env_step": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _F32, _F32, _PTR]),
 }
 
 

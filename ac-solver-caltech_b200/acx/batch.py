@@ -72,11 +72,13 @@ class EnvBuffers:
         dev = state.device
         self.state = state.contiguous()
         self.steps = torch.zeros(n, dtype=torch.int32, device=dev)
-        self.lens = torch.empty((n, 2), dtype=torch.uint8, device=dev)
-        self.reward = torch.empty(n, dtype=torch.int32, device=dev)
+        # one 8-byte record per env written by the kernel: int32 reward | done | truncated | len0 | len1
+        self.step_out = torch.zeros((n, 8), dtype=torch.uint8, device=dev)
+        self.reward = self.step_out.view(torch.int32)[:, 0]
+        self.done = self.step_out[:, 4]
+        self.truncated = self.step_out[:, 5]
+        self.lens = self.step_out[:, 6:8]
         self.reward_clipped = torch.empty(n, dtype=torch.float32, device=dev)
-        self.done = torch.empty(n, dtype=torch.uint8, device=dev)
-        self.truncated = torch.empty(n, dtype=torch.uint8, device=dev)
         self.status = torch.empty(n, dtype=torch.uint8, device=dev)
         self.pool = None if pool is None else pool.contiguous()
 
@@ -91,8 +93,7 @@ def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0)):
         if pool is None:
             raise ValueError("next_idx given but the env buffers hold no pool")
     rc = _lib.lib().acx_env_step(_ptr(buf.state), _ptr(buf.steps), _ptr(actions), _ptr(pool), _ptr(next_idx),
-                                 _ptr(buf.reward), _ptr(buf.reward_clipped), _ptr(buf.done), _ptr(buf.truncated),
-                                 _ptr(buf.lens), _ptr(buf.status), buf.n, buf.m, buf.horizon,
-                                 float(clip[0]), float(clip[1]), stream)
+                                 _ptr(buf.step_out), _ptr(buf.reward_clipped), _ptr(buf.status), buf.n, buf.m,
+                                 buf.horizon, float(clip[0]), float(clip[1]), stream)
     _lib.check(rc, "acx_env_step")
     return buf

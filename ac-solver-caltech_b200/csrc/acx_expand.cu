@@ -58,7 +58,14 @@ __global__ void __launch_bounds__(12 * PB) k_expand_simple(const ExpandParams p)
     if (pi < np) {
         int l0, l1;
         uint32_t st;
-        acmove_row<W, 0>(sp + (size_t)pi * rowb, sc + (size_t)tid * rowb, m, a, p.cyclical != 0, l0, l1, st);
+        uint8_t* child = sc + (size_t)tid * rowb;
+        if constexpr (W <= 2) {  // 64-bit planes work in place: seed the child slot with the parent
+            const uint8_t* par = sp + (size_t)pi * rowb;
+            for (int k = 0; k < rowb; ++k) child[k] = par[k];
+            acmove_row64<0>(child, m, a, p.cyclical != 0, l0, l1, st);
+        } else {
+            acmove_row<W, 0>(sp + (size_t)pi * rowb, child, m, a, p.cyclical != 0, l0, l1, st);
+        }
         const int64_t c = (f0 + pi) * 12 + a;
         if (p.lens) {
             p.lens[2 * c] = (uint8_t)l0;

@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/acx.h"
@@ -33,15 +34,20 @@ struct StepParams {
     int cyclical;
     // ACEnv.step extras (ENV kernels)
     int32_t* steps;
-    int32_t* reward;
+    uint8_t* step_out;  // [n, 8]: int32 reward | u8 done | u8 truncated | u8 len0 | u8 len1
     float* reward_clipped;
-    uint8_t* done;
-    uint8_t* truncated;
     const int8_t* pool;
     const int32_t* next_idx;
     int horizon;
     float clip_lo, clip_hi;
 };
+
+// m <= 64 takes the 64-bit plane path, wider rows the generic multi-word planes
+template <int W, int MS>
+__device__ __forceinline__ void row_move(uint8_t* srow, int m, int move, bool cyc, int& l0, int& l1, uint32_t& status) {
+    if constexpr (W <= 2) acmove_row64<MS>(srow, m, move, cyc, l0, l1, status);
+    else acmove_row<W, MS>(srow, srow, m, move, cyc, l0, l1, status);
+}
 
 // ac_env.py:97-111 on one row that already sits (post-move) in shared memory
 template <bool ENV>
@@ -56,14 +62,11 @@ __device__ __forceinline__ void row_epilogue(const StepParams& p, int64_t row, u
             b = b < 0 ? -b : b;
             done = (a == 1 && b == 2) || (a == 2 && b == 1);
         }
-        const int32_t max_reward = p.horizon * m * 2;          // ac_env.py:76
-        const int32_t rew = done ? max_reward : -total;        // ac_env.py:100
-        const int32_t steps = steps_in + 1;                    // ac_env.py:102
-        const bool trunc = steps >= p.horizon;                 // ac_env.py:103
-        p.reward[row] = rew;
+        const int32_t max_reward = p.horizon * m * 2;    // ac_env.py:76
+        const int32_t rew = done ? max_reward : -total;  // ac_env.py:100
+        const int32_t steps = steps_in + 1;              // ac_env.py:102
+        const bool trunc = steps >= p.horizon;           // ac_env.py:103
         if (p.reward_clipped) p.reward_clipped[row] = fminf(fmaxf((float)rew, p.clip_lo), p.clip_hi);
-        p.done[row] = done ? 1 : 0;
-        p.truncated[row] = trunc ? 1 : 0;
         int32_t steps_out = steps;
         if (p.pool && (done || trunc)) {  // ac_env.py:113-129 via agents/training.py:351-352
             const int8_t* src = p.pool + (int64_t)p.next_idx[row] * 2 * m;
@@ -80,8 +83,11 @@ __device__ __forceinline__ void row_epilogue(const StepParams& p, int64_t row, u
             steps_out = 0;
         }
         p.steps[row] = steps_out;
+        const uint32_t hi = (done ? 1u : 0u) | (trunc ? 0x100u : 0u) | ((uint32_t)l0 << 16) | ((uint32_t)l1 << 24);
+        reinterpret_cast<uint2*>(p.step_out)[row] = make_uint2((uint32_t)rew, hi);
+    } else {
+        if (p.lens) *reinterpret_cast<uchar2*>(p.lens + 2 * row) = make_uchar2((uint8_t)l0, (uint8_t)l1);
     }
-    if (p.lens) *reinterpret_cast<uchar2*>(p.lens + 2 * row) = make_uchar2((uint8_t)l0, (uint8_t)l1);
     if (p.status) p.status[row] = (uint8_t)status;
 }
 
@@ -131,7 +137,7 @@ __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t nti
         uint8_t* srow = smem + (size_t)s * TILEB + (size_t)tid * ROWB;
         int l0, l1;
         uint32_t status;
-        acmove_row<W, MS>(srow, srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
+        row_move<W, MS>(srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
         row_epilogue<ENV>(p, row, srow, MS, l0, l1, status, steps_in);
 
         fence_proxy_async();
@@ -185,7 +191,7 @@ __global__ void __launch_bounds__(TR) k_rows_simple(const StepParams p, int64_t 
         uint8_t* srow = smem + (size_t)tid * rowb;
         int l0, l1;
         uint32_t status;
-        acmove_row<W, MS>(srow, srow, m, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
+        row_move<W, MS>(srow, m, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
         row_epilogue<ENV>(p, row, srow, m, l0, l1, status, steps_in);
     }
     __syncthreads();
@@ -265,12 +271,21 @@ static int run_static(StepParams p, cudaStream_t st) {
     return ACX_OK;
 }
 
+static int tma_stages() {  // ACX_STAGES=3|4 (tuning knob; default 3)
+    static int v = 0;
+    if (v == 0) {
+        const char* e = getenv("ACX_STAGES");
+        v = (e && e[0] == '4') ? 4 : 3;
+    }
+    return v;
+}
+
 template <bool ENV>
 static int run_rows(StepParams p, cudaStream_t st) {
     if (p.n == 0) return ACX_OK;
     p.row0 = 0;
     switch (p.m) {
-        case 36: return run_static<2, 36, 128, 4, ENV>(p, st);
+        case 36: return tma_stages() == 3 ? run_static<2, 36, 128, 3, ENV>(p, st) : run_static<2, 36, 128, 4, ENV>(p, st);
         case 128: return run_static<4, 128, 64, 4, ENV>(p, st);
         default: break;
     }
@@ -301,29 +316,25 @@ extern "C" int acx_move_batch(const int8_t* states_in, const uint8_t* moves, int
 }
 
 extern "C" int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
-                            const int32_t* next_idx, int32_t* reward, float* reward_clipped, uint8_t* done,
-                            uint8_t* truncated, uint8_t* lens, uint8_t* row_status, int64_t n, int m, int horizon,
-                            float clip_lo, float clip_hi, acx_stream_t stream) {
+                            const int32_t* next_idx, uint8_t* step_out, float* reward_clipped, uint8_t* row_status,
+                            int64_t n, int m, int horizon, float clip_lo, float clip_hi, acx_stream_t stream) {
     if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH || horizon < 1)
         return acx_fail(ACX_ERR_ARG, "acx_env_step: need n >= 0, 1 <= m <= 128, horizon >= 1");
-    if (n > 0 && (!state || !steps || !actions || !reward || !done || !truncated))
-        return acx_fail(ACX_ERR_ARG, "acx_env_step: null pointer");
+    if (n > 0 && (!state || !steps || !actions || !step_out)) return acx_fail(ACX_ERR_ARG, "acx_env_step: null pointer");
+    if (((uintptr_t)step_out & 7u) != 0) return acx_fail(ACX_ERR_ARG, "acx_env_step: step_out must be 8-byte aligned");
     if ((pool == nullptr) != (next_idx == nullptr)) return acx_fail(ACX_ERR_ARG, "acx_env_step: pool and next_idx go together");
     StepParams p;
     memset(&p, 0, sizeof p);
     p.in = state;
     p.out = state;
     p.actions = actions;
-    p.lens = lens;
     p.status = row_status;
     p.n = n;
     p.m = m;
     p.cyclical = 1;
     p.steps = steps;
-    p.reward = reward;
+    p.step_out = step_out;
     p.reward_clipped = reward_clipped;
-    p.done = done;
-    p.truncated = truncated;
     p.pool = pool;
     p.next_idx = next_idx;
     p.horizon = horizon;

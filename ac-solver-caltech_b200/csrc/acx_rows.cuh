@@ -19,6 +19,13 @@ enum : uint32_t {
     ACX_ROW_INVALID_INPUT = 2   // not a valid presentation on input (utils.py:13-54)
 };
 
+// Result of classifying a packed row
+enum : int { ROW_FAST = 0, ROW_SLOW = 1, ROW_INVALID = 2 };
+
+}  // namespace acx
+#include "acx_rel64.cuh"
+namespace acx {
+
 // raw planes of one relator as read from memory
 template <int W>
 struct RawRel {
@@ -243,9 +250,6 @@ ACX_HD Rel<W> rel_select(bool second, const Rel<W>& r0, const Rel<W>& r1) {
     return o;
 }
 
-// Result of classifying a packed row
-enum : int { ROW_FAST = 0, ROW_SLOW = 1, ROW_INVALID = 2 };
-
 template <int W>
 ACX_HD int classify_row(const RawRel<W> (&raw)[2], uint32_t chk, Rel<W> (&r)[2], int (&cnt)[2]) {
     bool alpha_ok = (chk & 0x7C7C7C7Cu) == 0u;
@@ -332,6 +336,155 @@ ACX_HD void acmove_row(const uint8_t* in_row, uint8_t* out_row, int m_rt, int mo
     }
     l0 = r[0].n;
     l1 = r[1].n;
+}
+
+// =============================================================================================
+// m <= 64: the 64-bit plane path (acx_rel64.cuh).  Works IN PLACE on the row: only a relator whose
+// letters changed is written back (the other bytes already hold the right answer).
+// =============================================================================================
+template <int MS>
+ACX_HD void pack_row_static64(const uint8_t* row, Raw64 (&raw)[2], uint32_t& chk) {
+    constexpr int NW = MS / 4;
+    uint32_t w[2 * NW];
+    const uint2* p = reinterpret_cast<const uint2*>(row);
+#pragma unroll
+    for (int k = 0; k < NW; ++k) {
+        const uint2 v = p[k];
+        w[2 * k] = v.x;
+        w[2 * k + 1] = v.y;
+    }
+    chk = 0u;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        uint32_t b0[2] = {0u, 0u}, b1[2] = {0u, 0u}, s7[2] = {0u, 0u};
+#pragma unroll
+        for (int k = NW - 1; k >= 0; --k) pack_word(w[h * NW + k], b0[k / 8], b1[k / 8], s7[k / 8], chk);
+        raw[h].B0 = ((uint64_t)b0[1] << 32) | b0[0];
+        raw[h].B1 = ((uint64_t)b1[1] << 32) | b1[0];
+        raw[h].S7 = ((uint64_t)s7[1] << 32) | s7[0];
+    }
+}
+
+// planes -> letters of ONE relator, 32-bit stores (rel is 4-byte aligned)
+template <int MS>
+ACX_HD void unpack_rel_static64(uint8_t* rel, const R64& r) {
+    constexpr int NW = MS / 4;
+    const uint64_t N = mask64(r.n), X = r.S ^ r.T;
+    const uint32_t n2[2] = {(uint32_t)N, (uint32_t)(N >> 32)};
+    const uint32_t s2[2] = {(uint32_t)r.S, (uint32_t)(r.S >> 32)};
+    const uint32_t x2[2] = {(uint32_t)X, (uint32_t)(X >> 32)};
+    uint32_t* p = reinterpret_cast<uint32_t*>(rel);
+#pragma unroll
+    for (int k = 0; k < NW; ++k) {
+        const int g = k / 8, sh = 4 * (k % 8);
+        const uint32_t nn = (n2[g] >> sh) & 0xFu, ss = (s2[g] >> sh) & 0xFu, xx = (x2[g] >> sh) & 0xFu;
+        p[k] = spread4(nn) + spread4(xx) + 253u * spread4(ss);
+    }
+}
+
+ACX_HD void pack_rel_dynamic64(const uint8_t* rel, int m, Raw64& raw, uint32_t& chk) {
+    uint32_t b0[2] = {0u, 0u}, b1[2] = {0u, 0u}, s7[2] = {0u, 0u};
+    const int nw = (m + 3) >> 2;
+    for (int k = nw - 1; k >= 0; --k) {
+        uint32_t x = 0u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int idx = 4 * k + j;
+            const uint32_t b = (idx < m) ? (uint32_t)rel[idx] : 0u;
+            x |= b << (8 * j);
+        }
+        b0[1] = fshl(b0[0], b0[1], 4);
+        b1[1] = fshl(b1[0], b1[1], 4);
+        s7[1] = fshl(s7[0], s7[1], 4);
+        pack_word(x, b0[0], b1[0], s7[0], chk);
+    }
+    raw.B0 = ((uint64_t)b0[1] << 32) | b0[0];
+    raw.B1 = ((uint64_t)b1[1] << 32) | b1[0];
+    raw.S7 = ((uint64_t)s7[1] << 32) | s7[0];
+}
+
+ACX_HD void unpack_rel_dynamic64(uint8_t* rel, int m, const R64& r) {
+    uint64_t N = mask64(r.n), S = r.S, X = r.S ^ r.T;
+    const int nw = (m + 3) >> 2;
+    for (int k = 0; k < nw; ++k) {
+        const uint32_t x = spread4((uint32_t)N & 0xFu) + spread4((uint32_t)X & 0xFu) + 253u * spread4((uint32_t)S & 0xFu);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (4 * k + j < m) rel[4 * k + j] = (uint8_t)(x >> (8 * j));
+        N >>= 4;
+        S >>= 4;
+        X >>= 4;
+    }
+}
+
+// One ACMove on one row, in place.  MS > 0: static width (MS % 4 == 0, MS <= 64, row 8-byte
+// aligned); MS == 0: any 1 <= m <= 64.
+template <int MS>
+ACX_HD void acmove_row64(uint8_t* row, int m_rt, int move, bool cyc, int& l0, int& l1, uint32_t& status) {
+    const int m = MS ? MS : m_rt;
+    Raw64 raw[2];
+    uint32_t chk = 0u;
+    if (MS) {
+        pack_row_static64<(MS ? MS : 4)>(row, raw, chk);
+    } else {
+        pack_rel_dynamic64(row, m, raw[0], chk);
+        pack_rel_dynamic64(row + m, m, raw[1], chk);
+    }
+    R64 r[2];
+    int cnt[2];
+    const int cls = classify_row64(raw, chk, r, cnt);
+    if (cls == ROW_SLOW) {
+        slow_acmove(reinterpret_cast<const int8_t*>(row), reinterpret_cast<int8_t*>(row), m, move, cyc ? 1 : 0, l0, l1,
+                    status);
+        return;
+    }
+    l0 = cnt[0];
+    l1 = cnt[1];
+    if (cls == ROW_INVALID) {
+        status = ACX_ROW_INVALID_INPUT;
+        return;
+    }
+    const uint32_t d = decode_move(move);
+    const bool i = d & 1u, is_conj = d & 2u, inv = d & 4u;
+    R64 a, o;  // touched relator, other relator
+    a.S = i ? r[1].S : r[0].S;
+    a.T = i ? r[1].T : r[0].T;
+    a.n = i ? r[1].n : r[0].n;
+    o.S = i ? r[0].S : r[1].S;
+    o.T = i ? r[0].T : r[1].T;
+    o.n = i ? r[0].n : r[1].n;
+    bool a_changed, o_changed = false;
+    if (!is_conj) {
+        R64 b = o;
+        if (inv) b = r64_inverse(b);
+        a_changed = r64_concat(a, b, m);
+    } else {
+        a_changed = r64_conjugate(a, inv ? 1u : 0u, (d >> 3) & 1u, m);
+    }
+    if (a.n == 0) {  // utils.py:264-266 raises; row stays as it was
+        status = ACX_ROW_EMPTY_RELATOR;
+        return;
+    }
+    if (cyc) {
+        if (r64_cyclic_reduce(a) > 0) a_changed = true;
+        if (r64_needs_cyclic(o)) {
+            r64_cyclic_reduce(o);
+            o_changed = true;
+        }
+    }
+    uint8_t* pa = row + (i ? m : 0);
+    uint8_t* po = row + (i ? 0 : m);
+    if (a_changed) {
+        if (MS) unpack_rel_static64<(MS ? MS : 4)>(pa, a);
+        else unpack_rel_dynamic64(pa, m, a);
+    }
+    if (o_changed) {
+        if (MS) unpack_rel_static64<(MS ? MS : 4)>(po, o);
+        else unpack_rel_dynamic64(po, m, o);
+    }
+    l0 = i ? o.n : a.n;
+    l1 = i ? a.n : o.n;
+    status = ACX_ROW_OK;
 }
 
 }  // namespace acx

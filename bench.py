@@ -135,3 +135,200 @@ class ClockSampler:
         reasons = sorted({nm for r in rows for nm, v in zip(names, r[5:9]) if v.lower().startswith("active")})
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][2]), "reasons": reasons, "samples": len(rows),
                 "power_w_max": max(float(r[3]) for r in rows)}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_oracle_throughput(n_env, target_seconds, threads):
+    """transitions/s of the CPU oracle (C restatement of the reference) on a bounded sample."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ac_oracle
+
+    ac_oracle.build()
+    pool = load_pool()
+    rng = np.random.default_rng(0)
+    n = min(n_env, 1 << 18)
+    state = pool[rng.integers(0, len(pool), n)].copy()
+    steps = np.zeros(n, dtype=np.int32)
+    nxt = rng.integers(0, len(pool), n).astype(np.int32)
+    for _ in range(16):  # spread the lengths a little, untimed
+        ac_oracle.env_step_batch(state, steps, rng.integers(0, 12, n).astype(np.uint8), HORIZON, pool, nxt, threads)
+    acts = [rng.integers(0, 12, n).astype(np.uint8) for _ in range(8)]
+    done_steps, t0 = 0, time.perf_counter()
+    while True:
+        ac_oracle.env_step_batch(state, steps, acts[done_steps % 8], HORIZON, pool, nxt, threads)
+        done_steps += 1
+        dt = time.perf_counter() - t0
+        if dt >= target_seconds:
+            break
+    return n * done_steps / dt, "%d ACEnv.step passes over %d envs (m=36) in %.1f s" % (done_steps, n, dt)
+
+
+def reference_arm(args):
+    """--impl reference: the CPU implementation of the path on the host cores (rank 0 only).  The
+    reference itself is pure Python; what is timed here is its C restatement (oracle/), all cores."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ac_oracle
+
+    ac_oracle.build()
+    cores = os.cpu_count() or 1
+    pool = load_pool()
+    rng = np.random.default_rng(0)
+    n = min(args.envs, 1 << 18)
+    state = pool[rng.integers(0, len(pool), n)].copy()
+    steps = np.zeros(n, dtype=np.int32)
+    nxt = rng.integers(0, len(pool), n).astype(np.int32)
+    acts = [rng.integers(0, 12, n).astype(np.uint8) for _ in range(8)]
+    for k in range(max(args.warmup, 16)):
+        ac_oracle.env_step_batch(state, steps, acts[k % 8], HORIZON, pool, nxt, cores)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        ac_oracle.env_step_batch(state, steps, acts[k % 8], HORIZON, pool, nxt, cores)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "i8", "data": "synthetic", "config": config_dict(args.envs, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "each step = one lockstep ACEnv.step pass over %d envs (m=36) with the C oracle "
+                                   "(oracle/ac_oracle.c, pinned against the reference Python), %d pthreads" % (n, cores)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "the reference itself is pure Python (10.7k ACMove/s/core, SURVEY.md section 6); this arm times "
+                "its C restatement on all host cores, roughly 3 orders of magnitude faster than the reference",
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    from acx import batch, vecenv
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the AC-move engine has no CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.envs
+    pool_np = load_pool()
+    pool = torch.from_numpy(pool_np).to(dev)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    bufs, acts, nxts = [], [], []
+    for b in range(N_BATCHES):
+        states = walk_states_gpu(pool, n, seed=100 * rank + b, dev=dev)
+        bufs.append(batch.EnvBuffers(states, HORIZON, pool=pool))
+        bufs[-1].steps.copy_(torch.randint(0, HORIZON, (n,), device=dev, generator=g, dtype=torch.int32))
+        acts.append(torch.randint(0, 12, (n,), device=dev, generator=g, dtype=torch.int64).to(torch.uint8))
+        nxts.append(torch.randint(0, pool.shape[0], (n,), device=dev, generator=g, dtype=torch.int32))
+    before = bufs[0].state.clone()
+
+    def step(k):
+        b = k % N_BATCHES
+        batch.env_step(bufs[b], acts[(k // N_BATCHES) % N_BATCHES], next_idx=nxts[b])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for k in range(args.warmup):
+        step(k)
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.time()
+    e0.record()
+    for k in range(args.steps):
+        step(args.warmup + k)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    # keep the same kernel running ~1.2 s more (untimed) so that nvidia-smi sees the clocks under this load
+    t_hold = time.time()
+    k = 0
+    while time.time() - t_hold < 1.2:
+        for _ in range(50):
+            step(k)
+            k += 1
+        torch.cuda.synchronize()
+    clocks = sampler.stop(t_wall0, time.time())
+    changed = float((bufs[0].state != before).any(dim=1).float().mean().item())
+
+    # end to end through the host-buffer API (VecACEnv.step: numpy actions in, numpy results out)
+    env = vecenv.VecACEnv(pool_np, horizon_length=HORIZON, num_envs=n, device=str(dev),
+                          start_index=np.random.default_rng(rank).integers(0, len(pool_np), n))
+    env.reset()
+    env.buf.state.copy_(bufs[1].state)
+    host_actions = [np.random.default_rng(7 + i).integers(0, 12, n).astype(np.int64) for i in range(4)]
+    e2e_steps = max(3, min(args.steps, 20))
+    for i in range(3):
+        env.step(host_actions[i % 4])
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        env.step(host_actions[i % 4])
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+
+    tm = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(tm[0]), float(tm[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    value = world * n * args.steps / (ms * 1e-3)
+    kern_s = ms * 1e-3 / args.steps  # one launch per step
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = n * ALG_BYTES / kern_s / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "i8", "data": "synthetic", "config": config_dict(n, world),
+        "clocks": clocks,
+        "e2e": {"value": world * n * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": env.h2d_bytes_per_step, "d2h_bytes_per_step": env.d2h_bytes_per_step,
+                "api": "acx.vecenv.VecACEnv.step(numpy actions) -> numpy obs/reward/done/truncated", "steps": e2e_steps},
+        "gpu_launches": args.steps,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "k_rows_tma<2,36,128,4,ENV>",
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
+                     "alg_bytes_per_transition": ALG_BYTES},
+        "changed_row_fraction": changed,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        v, sample = cpu_oracle_throughput(n, 10.0 / max(1, cores) + 2.0, cores)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": sample + " (C oracle, %d pthreads; the reference itself is pure Python, "
+                                                   "about 1e4 ACMove/s/core)" % cores}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        reference_arm(a)
+    else:
+        gpu_arm(a)

@@ -61,12 +61,15 @@ int acx_move_batch(const int8_t* states_in, const uint8_t* moves, int8_t* states
  * max_reward = horizon*m*2 (:76), count_steps += 1, truncated = count_steps >= horizon), fused
  * with the reset the PPO loop applies to finished envs (ACEnv.reset, ac_env.py:113-129;
  * agents/training.py:351-352): when pool != NULL and done|truncated, state <- pool[next_idx[e]],
- * steps <- 0.  reward_clipped (optional) = clip(reward, clip_lo, clip_hi), the TransformReward
- * wrapper of agents/environment.py:48-52.  lens [n,2], row_status [n] may be NULL. */
+ * steps <- 0.
+ * step_out [n] is one 8-byte record per env (8-byte aligned):
+ *     int32 reward | uint8 done | uint8 truncated | uint8 len(r_0) | uint8 len(r_1)
+ * (lengths are those of the state left in `state`, i.e. after a reset if one happened).
+ * reward_clipped (optional, float [n]) = clip(reward, clip_lo, clip_hi), the TransformReward
+ * wrapper of agents/environment.py:48-52.  row_status [n] may be NULL. */
 int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
-                 const int32_t* next_idx, int32_t* reward, float* reward_clipped, uint8_t* done,
-                 uint8_t* truncated, uint8_t* lens, uint8_t* row_status, int64_t n, int m, int horizon,
-                 float clip_lo, float clip_hi, acx_stream_t stream);
+                 const int32_t* next_idx, uint8_t* step_out, float* reward_clipped, uint8_t* row_status,
+                 int64_t n, int m, int horizon, float clip_lo, float clip_hi, acx_stream_t stream);
 
 /* All 12 successors of every parent in one launch -- the `for action in range(12)` loops of
  * ac_solver/search/greedy.py:76-83 and ac_solver/search/breadth_first.py:69-76.

@@ -30,9 +30,38 @@ static void run(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* le
     }
 }
 
-// variant: 0 = dynamic width, 1 = static instantiation (m must be 36 or 128)
+template <int MS>
+static void run64(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status, int64_t n, int m,
+                  int cyc) {
+    const int rowb = 2 * m;
+    std::vector<uint64_t> a(rowb / 8 + 2);
+    for (int64_t r = 0; r < n; ++r) {
+        uint8_t* ia = reinterpret_cast<uint8_t*>(a.data());
+        memcpy(ia, in + r * rowb, rowb);
+        int l0 = -1, l1 = -1;
+        uint32_t st = 99;
+        acmove_row64<MS>(ia, m, moves[r], cyc != 0, l0, l1, st);
+        memcpy(out + r * rowb, ia, rowb);
+        lens[2 * r] = (uint8_t)l0;
+        lens[2 * r + 1] = (uint8_t)l1;
+        status[r] = (uint8_t)st;
+    }
+}
+
+// variant: 0 = dynamic width (generic planes), 1 = static generic planes (m must be 36 or 128),
+//          2 = 64-bit planes dynamic (m <= 64), 3 = 64-bit planes static (m == 36)
 extern "C" int acxh_move_batch(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status,
                                int64_t n, int m, int cyc, int variant, int inplace) {
+    if (variant == 2) {
+        if (m > 64) return -1;
+        run64<0>(in, moves, out, lens, status, n, m, cyc);
+        return 0;
+    }
+    if (variant == 3) {
+        if (m != 36) return -1;
+        run64<36>(in, moves, out, lens, status, n, m, cyc);
+        return 0;
+    }
     if (variant == 1) {
         if (m == 36) run<2, 36>(in, moves, out, lens, status, n, m, cyc, inplace);
         else if (m == 128) run<4, 128>(in, moves, out, lens, status, n, m, cyc, inplace);

@@ -10,7 +10,15 @@ from host_harness import harness
 
 
 def _variants(m):
-    return (0, 1) if m in (36, 128) else (0,)
+    """0/1: generic multi-word planes (dynamic / static); 2/3: 64-bit planes (dynamic / static 36)"""
+    v = [0]
+    if m in (36, 128):
+        v.append(1)
+    if m <= 64:
+        v.append(2)
+    if m == 36:
+        v.append(3)
+    return v
 
 
 @pytest.mark.parametrize("m", [4, 7, 18, 36, 128])
