@@ -19,6 +19,9 @@ _SIGNATURES = {
     "acx_set_device": (_I32, [_I32]),
     "acx_move_batch": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR]),
     "acx_expand12": (_I32, [_PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR]),
+    "acx_search_workspace_bytes": (_I64, [_I32, _I32, _I64]),
+    "acx_search_batch": (_I32, [_PTR, _I32, _I32, _I64, _I32, _I32, _PTR, _I64, _PTR, _PTR, _I32, _PTR]),
+    "acx_rows_primitive": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR]),
     "acx_env_step": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _F32, _F32, _PTR]),
 }
 

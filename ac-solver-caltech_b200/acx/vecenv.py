@@ -20,6 +20,56 @@ import torch
 from . import batch
 
 
+class _EnvHandle:
+    """`envs.envs[i]`: what the PPO loop pokes at for a single env (agents/training.py:352)."""
+
+    def __init__(self, vec, index):
+        self._vec, self._i = vec, index
+
+    def reset(self, *, seed=None, options=None):
+        v, i = self._vec, self._i
+        if options and "starting_state" in options:
+            row = torch.from_numpy(np.ascontiguousarray(np.asarray(options["starting_state"]), dtype=np.int8)).to(v.device)
+        else:
+            row = v.pool[int(v.start_index[i])]
+        v.buf.state[i].copy_(row)
+        v.buf.steps[i] = 0
+        m = v.max_relator_length
+        v.buf.lens[i, 0] = int((row[:m] != 0).sum())
+        v.buf.lens[i, 1] = int((row[m:] != 0).sum())
+        return v.buf.state[i].cpu().numpy(), {}
+
+    @property
+    def state(self):
+        return self._vec.buf.state[self._i].cpu().numpy()
+
+    @property
+    def lengths(self):
+        return [int(x) for x in self._vec.buf.lens[self._i].cpu().numpy()]
+
+    @property
+    def count_steps(self):
+        return int(self._vec.buf.steps[self._i])
+
+
+class _LazyHandles:
+    """envs.envs[i] for very large batches without materialising N Python objects."""
+
+    def __init__(self, vec):
+        self._vec = vec
+
+    def __getitem__(self, i):
+        return _EnvHandle(self._vec, i)
+
+    def __len__(self):
+        return self._vec.num_envs
+
+
+class _Space:
+    def __init__(self, shape=None, n=None, dtype=None):
+        self.shape, self.n, self.dtype = shape, n, dtype
+
+
 class VecACEnv:
     def __init__(self, initial_states, horizon_length=1000, num_envs=None, start_index=None, device="cuda:0",
                  clip_rewards=True, min_rew=-10.0, max_rew=1000.0):
@@ -40,16 +90,18 @@ class VecACEnv:
         # where each env restarts when it finishes (device resident; update with set_next_states)
         self.next_state_index = self.start_index.to(torch.int32).contiguous()
         self.buf = None
+        self.envs = [_EnvHandle(self, i) for i in range(n)] if n <= 4096 else _LazyHandles(self)
+        self.single_observation_space = _Space(shape=(pool.shape[1],), dtype=np.int8)
+        self.single_action_space = _Space(n=12)
         # pinned host staging for the numpy API
         row = pool.shape[1]
         self._h_act = torch.empty(n, dtype=torch.uint8).pin_memory()
         self._h_obs = torch.empty((n, row), dtype=torch.int8).pin_memory()
         self._h_rew = torch.empty(n, dtype=torch.float32).pin_memory()
-        self._h_done = torch.empty(n, dtype=torch.uint8).pin_memory()
-        self._h_trunc = torch.empty(n, dtype=torch.uint8).pin_memory()
+        self._h_out = torch.empty((n, 8), dtype=torch.uint8).pin_memory()  # reward | done | truncated | lens
         self._d_act = torch.empty(n, dtype=torch.uint8, device=self.device)
         self.h2d_bytes_per_step = n
-        self.d2h_bytes_per_step = n * row + 4 * n + n + n
+        self.d2h_bytes_per_step = n * row + 4 * n + 8 * n
 
     # -- gymnasium-vector-like surface --------------------------------------------------------
     def reset(self, seed=None, options=None):
@@ -67,18 +119,18 @@ class VecACEnv:
         return b.state, b.reward_clipped, b.done, b.truncated
 
     def step(self, actions):
-        """numpy actions [N] (any int dtype) -> (obs int8 [N,2m], reward f32, done bool, truncated bool, {})."""
+        """numpy actions [N] (any int dtype) -> (obs int8 [N,2m], reward f32, done bool, truncated bool, {}).
+        The returned arrays are views of pinned staging buffers that the next step overwrites."""
         a = np.asarray(actions)
         self._h_act.numpy()[:] = a  # dtype conversion into pinned memory
         self._d_act.copy_(self._h_act, non_blocking=True)
         b = batch.env_step(self.buf, self._d_act, next_idx=self.next_state_index, clip=self.clip)
         self._h_obs.copy_(b.state, non_blocking=True)
         self._h_rew.copy_(b.reward_clipped, non_blocking=True)
-        self._h_done.copy_(b.done, non_blocking=True)
-        self._h_trunc.copy_(b.truncated, non_blocking=True)
+        self._h_out.copy_(b.step_out, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
-        return (self._h_obs.numpy(), self._h_rew.numpy(), self._h_done.numpy().view(np.bool_),
-                self._h_trunc.numpy().view(np.bool_), {})
+        rec = self._h_out.numpy()
+        return (self._h_obs.numpy(), self._h_rew.numpy(), rec[:, 4].view(np.bool_), rec[:, 5].view(np.bool_), {})
 
     @property
     def lengths(self):

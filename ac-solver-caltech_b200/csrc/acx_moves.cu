@@ -198,6 +198,21 @@ __global__ void __launch_bounds__(TR) k_rows_simple(const StepParams p, int64_t 
     coop_copy(gout, smem, rows * rowb, tid, TR);
 }
 
+// scalar-API helper: one thread per row straight on global memory, byte path only
+__global__ void k_rows_primitive(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status,
+                                 int64_t n, int m, int mode) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    int l0, l1;
+    uint32_t st;
+    slow_acmove(in + row * 2 * m, out + row * 2 * m, m, moves ? moves[row] : 0, mode, l0, l1, st);
+    if (lens) {
+        lens[2 * row] = (uint8_t)l0;
+        lens[2 * row + 1] = (uint8_t)l1;
+    }
+    if (status) status[row] = (uint8_t)st;
+}
+
 // ---------------------------------------------------------------------------------------------
 static int current_device() {
     int dev = 0;
@@ -341,4 +356,16 @@ extern "C" int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* action
     p.clip_lo = clip_lo;
     p.clip_hi = clip_hi;
     return run_rows<true>(p, (cudaStream_t)stream);
+}
+
+extern "C" int acx_rows_primitive(const int8_t* states_in, const uint8_t* moves, int8_t* states_out, uint8_t* lens_out,
+                                  uint8_t* row_status, int64_t n, int m, int mode, acx_stream_t stream) {
+    if (n < 0 || m < 1 || m > 4096) return acx_fail(ACX_ERR_ARG, "acx_rows_primitive: need n >= 0 and 1 <= m <= 4096");
+    if (n > 0 && (!states_in || !states_out)) return acx_fail(ACX_ERR_ARG, "acx_rows_primitive: null pointer");
+    if (!(mode & ACX_MODE_NO_MOVE) && n > 0 && !moves) return acx_fail(ACX_ERR_ARG, "acx_rows_primitive: moves missing");
+    if (n == 0) return ACX_OK;
+    k_rows_primitive<<<(unsigned)((n + 63) / 64), 64, 0, (cudaStream_t)stream>>>(states_in, moves, states_out, lens_out,
+                                                                              row_status, n, m, mode);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
 }

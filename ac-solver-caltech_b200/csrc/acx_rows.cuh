@@ -137,6 +137,9 @@ ACX_HD void unpack_rel_dynamic(uint8_t* rel, int m, const Rel<W>& r) {
 // ---- byte-wise slow path: literal restatement of the reference on one row ---------------
 // Taken only for rows with letters outside {0,+-1,+-2} or with a non-reduced relator.
 // `in` and `out` may be the same buffer.
+// mode: bit 0 = cyclic reduction; bit 1 = no move (simplify_presentation only, utils.py:246-283);
+//       bit 2 = move only (concatenate_relators / conjugate as the reference exposes them:
+//       junction cancellation + guard, no validity assert, no reduction).
 // Follows ac_moves.py:4-156 (move, junction cancel, guard), utils.py:264-266 (validity),
 // utils.py:211-232 (stack free reduction, cyclic reduction).
 static __host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_t* out, int m, int move, int cyc,
@@ -161,13 +164,16 @@ static __host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_
         status = ACX_ROW_INVALID_INPUT;
         return;
     }
-    const uint32_t d = decode_move(move);
+    const int raw = (cyc >> 2) & 1, no_move = (cyc >> 1) & 1;
+    cyc &= 1;
+    const uint32_t d = decode_move(no_move ? 0 : move);
     const int i = d & 1, is_conj = (d >> 1) & 1, inv = (d >> 2) & 1, gy = (d >> 3) & 1;
     int8_t* a = out + i * m;
     const int8_t* b = in + (1 - i) * m;
     int la = cnt[i];
     const int lb = cnt[1 - i];
-    if (!is_conj) {
+    if (no_move) {
+    } else if (!is_conj) {
         int acc = 0;
         const int lim = la < lb ? la : lb;
         while (acc < lim) {
@@ -177,7 +183,7 @@ static __host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_
             ++acc;
         }
         const int nn = la + lb - 2 * acc;
-        if (nn == 0) {  // utils.py:264-266 would raise; row is handed back unchanged
+        if (nn == 0 && !raw) {  // utils.py:264-266 would raise; row is handed back unchanged
             status = ACX_ROW_EMPTY_RELATOR;
             return;
         }
@@ -191,7 +197,7 @@ static __host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_
         const int g = (gy ? 2 : 1) * (inv ? -1 : 1);
         const int sc = ((int)a[0] == -g), ec = ((int)a[la - 1] == g);
         const int nn = la + 2 - 2 * (sc + ec);
-        if (nn == 0) {
+        if (nn == 0 && !raw) {
             status = ACX_ROW_EMPTY_RELATOR;
             return;
         }
@@ -210,6 +216,12 @@ static __host__ __device__ __noinline__ void slow_acmove(const int8_t* in, int8_
             for (int k = pos; k < m; ++k) a[k] = 0;
             la = nn;
         }
+    }
+    if (raw) {
+        l0 = i ? cnt[0] : la;
+        l1 = i ? la : cnt[1];
+        status = ACX_ROW_OK;
+        return;
     }
     int len[2];
     for (int h = 0; h < 2; ++h) {

@@ -56,6 +56,20 @@ int acx_set_device(int dev);
 int acx_move_batch(const int8_t* states_in, const uint8_t* moves, int8_t* states_out, uint8_t* lens_out,
                    uint8_t* row_status, int64_t n, int m, int cyclical, acx_stream_t stream);
 
+/* The word-arithmetic primitives the reference exposes next to ACMove, for its scalar API and tests
+ * (symbol-agnostic byte path, any non-zero int8 letters, 1 <= m <= 4096):
+ *   mode = ACX_MODE_NO_MOVE [| ACX_MODE_CYCLICAL]   simplify_presentation (utils.py:246-283)
+ *   mode = ACX_MODE_RAW_MOVE                        concatenate_relators / conjugate only
+ *                                                   (ac_moves.py:4-156; moves[] = the id of the
+ *                                                   ACMove that uses that primitive), no reduction
+ *   mode = 0 | ACX_MODE_CYCLICAL                    full ACMove, byte path
+ * states_out may alias states_in. */
+#define ACX_MODE_CYCLICAL 1
+#define ACX_MODE_NO_MOVE 2
+#define ACX_MODE_RAW_MOVE 4
+int acx_rows_primitive(const int8_t* states_in, const uint8_t* moves, int8_t* states_out, uint8_t* lens_out,
+                       uint8_t* row_status, int64_t n, int m, int mode, acx_stream_t stream);
+
 /* ACEnv.step in lockstep, in place -- ac_solver/envs/ac_env.py:91-111 (cyclical=True move,
  * done = total length 2 and trivial, reward = max_reward*done - total*(1-done) with
  * max_reward = horizon*m*2 (:76), count_steps += 1, truncated = count_steps >= horizon), fused
@@ -76,6 +90,21 @@ int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const in
  * children [f,12,2m], child_lens [f,12,2], child_status [f,12] (the last two may be NULL). */
 int acx_expand12(const int8_t* parents, int8_t* children, uint8_t* child_lens, uint8_t* child_status,
                  int64_t f, int m, int cyclical, acx_stream_t stream);
+
+/* greedy_search / bfs for a batch of independent instances (one root each, same m) in ONE launch --
+ * ac_solver/search/greedy.py:15-121 (greedy = 1) and ac_solver/search/breadth_first.py:15-97
+ * (greedy = 0).  budget = max_nodes_to_explore, cyclical = cyclically_reduce_after_moves.
+ * workspace: device scratch of at least acx_search_workspace_bytes(n_instances, m, budget) bytes.
+ * result [n_instances, 8] int32: solved, len(tree_nodes) at exit, nodes expanded, path length
+ *   (0 = no path: bfs failure returns None; < 0 = path_cap too small, |value| needed), error (1 = a
+ *   relator became empty: the reference raises AssertionError), last popped node, last action, last
+ *   child length.
+ * path [n_instances, path_cap, 2] int32: (action, total length) pairs starting with (-1, len(root)),
+ *   exactly the list the reference returns (for a failed greedy search: its last expansion). */
+int64_t acx_search_workspace_bytes(int n_instances, int m, int64_t budget);
+int acx_search_batch(const int8_t* roots, int n_instances, int m, int64_t budget, int cyclical, int greedy,
+                     void* workspace, int64_t workspace_bytes, int32_t* result, int32_t* path, int path_cap,
+                     acx_stream_t stream);
 
 #ifdef __cplusplus
 }
