@@ -115,12 +115,12 @@ def test_search_vs_oracle_random(cuda, oracle, golden_dir):
     from acx import search
     from helpers import dataset_rows
 
-    rows = dataset_rows(golden_dir)
+    rows = [r for r in dataset_rows(golden_dir) if len(r) == 36]  # the m=18 block
     rng = np.random.default_rng(3)
     for greedy in (True, False):
         for cyc in (False, True):
             for budget in (1, 13, 500, 3000):
-                idx = [int(k) for k in rng.choice(340, size=12, replace=False)]  # the m=18 block
+                idx = [int(k) for k in rng.choice(len(rows), size=12, replace=False)]
                 res, paths = search.search_batch(np.stack([rows[k] for k in idx]), budget, cyc, greedy, str(cuda))
                 for j, k in enumerate(idx):
                     stats = {}
