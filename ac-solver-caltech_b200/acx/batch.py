@@ -62,6 +62,20 @@ def expand12(parents, cyclical=False, want_lens=True, want_status=True):
     return children, lens, status
 
 
+def certify(rows, lens_out=None):
+    """acx_rows_certify: True iff every row is certified; writes the lengths into lens_out (u8 [N,2] view)."""
+    n, row = rows.shape
+    _chk(rows, torch.int8, (n, row), "rows")
+    stream = _prep(rows.device)
+    lens = torch.empty((n, 2), dtype=torch.uint8, device=rows.device)
+    cert = torch.empty((n,), dtype=torch.uint8, device=rows.device)
+    rc = _lib.lib().acx_rows_certify(_ptr(rows), n, row // 2, _ptr(lens), _ptr(cert), stream)
+    _lib.check(rc, "acx_rows_certify")
+    if lens_out is not None:
+        lens_out.copy_(lens)
+    return bool(cert.all().item()) if n else True
+
+
 class EnvBuffers:
     """Device-resident state of N lockstep ACEnv instances (ac_env.py:53-89 fields, as arrays)."""
 
@@ -79,8 +93,25 @@ class EnvBuffers:
         self.truncated = self.step_out[:, 5]
         self.lens = self.step_out[:, 6:8]
         self.reward_clipped = torch.empty(n, dtype=torch.float32, device=dev)
+        # certification: when every state and pool row is certified the kernel skips its input checks
+        self.certified = certify(self.state, self.step_out[:, 6:8])
+        if self.certified and pool is not None:
+            self.certified = certify(pool.contiguous(), None)
         self.status = torch.empty(n, dtype=torch.uint8, device=dev)
         self.pool = None if pool is None else pool.contiguous()
+
+
+def _set_state(self, state, steps=None):
+    """Overwrite the env states (and optionally step counters); lengths and certification are redone."""
+    self.state.copy_(state)
+    if steps is not None:
+        self.steps.copy_(steps)
+    self.certified = certify(self.state, self.step_out[:, 6:8])
+    if self.certified and self.pool is not None:
+        self.certified = certify(self.pool, None)
+
+
+EnvBuffers.set_state = _set_state
 
 
 def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0)):
@@ -94,6 +125,7 @@ def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0)):
             raise ValueError("next_idx given but the env buffers hold no pool")
     rc = _lib.lib().acx_env_step(_ptr(buf.state), _ptr(buf.steps), _ptr(actions), _ptr(pool), _ptr(next_idx),
                                  _ptr(buf.step_out), _ptr(buf.reward_clipped), _ptr(buf.status), buf.n, buf.m,
-                                 buf.horizon, float(clip[0]), float(clip[1]), stream)
+                                 buf.horizon, float(clip[0]), float(clip[1]),
+                                 1 if buf.certified else 0, stream)
     _lib.check(rc, "acx_env_step")
     return buf

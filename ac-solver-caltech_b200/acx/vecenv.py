@@ -37,6 +37,8 @@ class _EnvHandle:
         m = v.max_relator_length
         v.buf.lens[i, 0] = int((row[:m] != 0).sum())
         v.buf.lens[i, 1] = int((row[m:] != 0).sum())
+        if v.buf.certified and not batch.certify(row[None, :].contiguous()):
+            v.buf.certified = False  # an arbitrary starting state: back to the checked kernel
         return v.buf.state[i].cpu().numpy(), {}
 
     @property

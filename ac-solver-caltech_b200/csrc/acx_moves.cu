@@ -40,6 +40,7 @@ struct StepParams {
     const int32_t* next_idx;
     int horizon;
     float clip_lo, clip_hi;
+    int certified;  // ACX_ENV_CERTIFIED: rows are certified and step_out holds their lengths
 };
 
 // m <= 64 takes the 64-bit plane path, wider rows the generic multi-word planes
@@ -92,7 +93,7 @@ __device__ __forceinline__ void row_epilogue(const StepParams& p, int64_t row, u
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int W, int MS, int TR, int S, bool ENV>
+template <int W, int MS, int TR, int S, bool ENV, bool CERT>
 __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t ntiles) {
     constexpr int ROWB = 2 * MS;
     constexpr uint32_t TILEB = (uint32_t)TR * ROWB;
@@ -132,12 +133,18 @@ __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t nti
         const int move = p.actions[row];
         int32_t steps_in = 0;
         if (ENV) steps_in = p.steps[row];
+        int l0 = 0, l1 = 0;
+        if (CERT) {  // lengths of a certified env row = the record the previous step left
+            const uchar2 ln = *reinterpret_cast<const uchar2*>(p.step_out + 8 * row + 6);
+            l0 = ln.x;
+            l1 = ln.y;
+        }
         mbar_wait(bar0 + 8 * s, parity);
 
         uint8_t* srow = smem + (size_t)s * TILEB + (size_t)tid * ROWB;
-        int l0, l1;
         uint32_t status;
-        row_move<W, MS>(srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
+        if constexpr (CERT) status = acmove_row64_certified<MS>(srow, move, l0, l1);
+        else row_move<W, MS>(srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
         row_epilogue<ENV>(p, row, srow, MS, l0, l1, status, steps_in);
 
         fence_proxy_async();
@@ -213,6 +220,28 @@ __global__ void k_rows_primitive(const int8_t* in, const uint8_t* moves, int8_t*
     if (status) status[row] = (uint8_t)st;
 }
 
+// certification of rows (see acx_rows.cuh): one thread per row on global memory
+__global__ void k_rows_certify(const int8_t* rows, int64_t n, int m, uint8_t* lens, uint8_t* cert) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    int l0 = 0, l1 = 0;
+    bool ok = false;
+    const uint8_t* r = reinterpret_cast<const uint8_t*>(rows) + row * 2 * m;
+    if (m <= 64) {
+        ok = row_is_certified(r, m, l0, l1);
+    } else {
+        for (int k = 0; k < m; ++k) {
+            l0 += r[k] != 0;
+            l1 += r[m + k] != 0;
+        }
+    }
+    if (lens) {
+        lens[2 * row] = (uint8_t)l0;
+        lens[2 * row + 1] = (uint8_t)l1;
+    }
+    if (cert) cert[row] = ok ? 1 : 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 static int current_device() {
     int dev = 0;
@@ -231,10 +260,10 @@ static int sm_count() {
     return cached[dev];
 }
 
-template <int W, int MS, int TR, int S, bool ENV>
+template <int W, int MS, int TR, int S, bool ENV, bool CERT>
 static int launch_tma(const StepParams& p, int64_t ntiles, cudaStream_t st) {
     constexpr size_t smem = (size_t)S * TR * 2 * MS + 8 * S;
-    auto kern = k_rows_tma<W, MS, TR, S, ENV>;
+    auto kern = k_rows_tma<W, MS, TR, S, ENV, CERT>;
     static int ctas_per_sm[ACX_MAX_DEVICES] = {0};  // function attributes are per device
     const int dev = current_device();
     if (ctas_per_sm[dev] == 0) {
@@ -275,7 +304,13 @@ static int run_static(StepParams p, cudaStream_t st) {
     if (aligned && p.n >= TR) {
         const int64_t ntiles = p.n / TR;
         p.row0 = 0;
-        int rc = launch_tma<W, MS, TR, S, ENV>(p, ntiles, st);
+        int rc;
+        if constexpr (ENV && W <= 2) {
+            rc = p.certified ? launch_tma<W, MS, TR, S, ENV, true>(p, ntiles, st)
+                             : launch_tma<W, MS, TR, S, ENV, false>(p, ntiles, st);
+        } else {
+            rc = launch_tma<W, MS, TR, S, ENV, false>(p, ntiles, st);
+        }
         if (rc) return rc;
         done_rows = ntiles * TR;
     }
@@ -332,7 +367,7 @@ extern "C" int acx_move_batch(const int8_t* states_in, const uint8_t* moves, int
 
 extern "C" int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
                             const int32_t* next_idx, uint8_t* step_out, float* reward_clipped, uint8_t* row_status,
-                            int64_t n, int m, int horizon, float clip_lo, float clip_hi, acx_stream_t stream) {
+                            int64_t n, int m, int horizon, float clip_lo, float clip_hi, int flags, acx_stream_t stream) {
     if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH || horizon < 1)
         return acx_fail(ACX_ERR_ARG, "acx_env_step: need n >= 0, 1 <= m <= 128, horizon >= 1");
     if (n > 0 && (!state || !steps || !actions || !step_out)) return acx_fail(ACX_ERR_ARG, "acx_env_step: null pointer");
@@ -355,6 +390,7 @@ extern "C" int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* action
     p.horizon = horizon;
     p.clip_lo = clip_lo;
     p.clip_hi = clip_hi;
+    p.certified = (flags & ACX_ENV_CERTIFIED) ? 1 : 0;
     return run_rows<true>(p, (cudaStream_t)stream);
 }
 
@@ -366,6 +402,16 @@ extern "C" int acx_rows_primitive(const int8_t* states_in, const uint8_t* moves,
     if (n == 0) return ACX_OK;
     k_rows_primitive<<<(unsigned)((n + 63) / 64), 64, 0, (cudaStream_t)stream>>>(states_in, moves, states_out, lens_out,
                                                                               row_status, n, m, mode);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+extern "C" int acx_rows_certify(const int8_t* rows, int64_t n, int m, uint8_t* lens_out, uint8_t* certified_out,
+                                acx_stream_t stream) {
+    if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH) return acx_fail(ACX_ERR_ARG, "acx_rows_certify: need n >= 0, 1 <= m <= 128");
+    if (n == 0) return ACX_OK;
+    if (!rows) return acx_fail(ACX_ERR_ARG, "acx_rows_certify: null pointer");
+    k_rows_certify<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(rows, n, m, lens_out, certified_out);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }

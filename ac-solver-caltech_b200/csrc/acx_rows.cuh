@@ -499,4 +499,98 @@ ACX_HD void acmove_row64(uint8_t* row, int m_rt, int move, bool cyc, int& l0, in
     status = ACX_ROW_OK;
 }
 
+// =============================================================================================
+// CERTIFIED rows (env state owned by the engine).  A row is certified when its letters are in
+// {0,+-1,+-2}, zeros only pad on the right, and both relators are freely AND cyclically reduced;
+// every ACMove(cyclical=True) output has these properties, so an env whose initial states are
+// certified (acx_rows_certify) stays certified for ever and its lengths are known.  Then:
+//   * the non-zero plane is mask(len): two planes per word instead of three, no classification;
+//   * conjugation of a cyclically reduced word by g is a rotation (first letter == g^-1: rotate
+//     left; last letter == g: rotate right) or the identity -- g a g^-1 reduces straight back to a,
+//     and the length guard cannot reject a rotation (ac_moves.py:119-126 + utils.py:223-232);
+//   * the untouched relator never changes.
+// Results are identical to acmove_row64 on certified rows (tests/test_gpu_moves.py, host harness).
+// =============================================================================================
+ACX_HD void pack_word2(uint32_t x, uint32_t& b0, uint32_t& s7) {
+    b0 = nib_push((x & 0x01010101u) * 0x10204080u, b0);
+    s7 = nib_push((x & 0x80808080u) * 0x00204081u, s7);
+}
+
+template <int MS>
+ACX_HD uint32_t acmove_row64_certified(uint8_t* row, int move, int& l0, int& l1) {
+    constexpr int NW = MS / 4;
+    uint32_t w[2 * NW];
+    const uint2* p = reinterpret_cast<const uint2*>(row);
+#pragma unroll
+    for (int k = 0; k < NW; ++k) {
+        const uint2 v = p[k];
+        w[2 * k] = v.x;
+        w[2 * k + 1] = v.y;
+    }
+    R64 r[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        uint32_t b0[2] = {0u, 0u}, s7[2] = {0u, 0u};
+#pragma unroll
+        for (int k = NW - 1; k >= 0; --k) pack_word2(w[h * NW + k], b0[k / 8], s7[k / 8]);
+        const int n = h ? l1 : l0;
+        const uint64_t B0 = ((uint64_t)b0[1] << 32) | b0[0];
+        r[h].S = ((uint64_t)s7[1] << 32) | s7[0];
+        r[h].T = ~B0 & mask64(n);  // x / x^-1 have bit 0 set, y / y^-1 do not
+        r[h].n = n;
+    }
+    const uint32_t d = decode_move(move);
+    const bool i = d & 1u, is_conj = d & 2u, inv = d & 4u;
+    R64 a, o;
+    a.S = i ? r[1].S : r[0].S;
+    a.T = i ? r[1].T : r[0].T;
+    a.n = i ? r[1].n : r[0].n;
+    o.S = i ? r[0].S : r[1].S;
+    o.T = i ? r[0].T : r[1].T;
+    o.n = i ? r[0].n : r[1].n;
+    bool changed;
+    if (!is_conj) {
+        R64 b = o;
+        if (inv) b = r64_inverse(b);
+        changed = r64_concat(a, b, MS);
+        if (a.n == 0) return ACX_ROW_EMPTY_RELATOR;  // utils.py:264-266 raises; row stays as it was
+        if (changed) r64_cyclic_reduce(a);
+    } else {
+        const uint32_t gs = inv ? 1u : 0u, gt = (d >> 3) & 1u;
+        const int n = a.n;
+        const uint32_t s0 = (uint32_t)a.S & 1u, t0 = (uint32_t)a.T & 1u;
+        const uint32_t sl = (uint32_t)shr64(a.S, n - 1) & 1u, tl = (uint32_t)shr64(a.T, n - 1) & 1u;
+        const bool sc = (t0 == gt) && (s0 != gs);  // first letter == g^-1: a[1:] + [g^-1]
+        const bool ec = (tl == gt) && (sl == gs);  // last letter == g:     [g] + a[:-1]
+        changed = (sc || ec) && n > 1;
+        if (sc) {
+            a.S = (a.S >> 1) | shl64((uint64_t)s0, n - 1);
+            a.T = (a.T >> 1) | shl64((uint64_t)t0, n - 1);
+        } else if (ec) {
+            const uint64_t mk = mask64(n);
+            a.S = ((a.S << 1) & mk) | (uint64_t)sl;
+            a.T = ((a.T << 1) & mk) | (uint64_t)tl;
+        }
+    }
+    if (changed) unpack_rel_static64<MS>(row + (i ? MS : 0), a);
+    l0 = i ? o.n : a.n;
+    l1 = i ? a.n : o.n;
+    return ACX_ROW_OK;
+}
+
+// is this row certified (see above)?  Also returns the relator lengths (non-zero counts).
+ACX_HD bool row_is_certified(const uint8_t* row, int m, int& l0, int& l1) {
+    Raw64 raw[2];
+    uint32_t chk = 0u;
+    pack_rel_dynamic64(row, m, raw[0], chk);
+    pack_rel_dynamic64(row + m, m, raw[1], chk);
+    R64 r[2];
+    int cnt[2];
+    const int cls = classify_row64(raw, chk, r, cnt);
+    l0 = cnt[0];
+    l1 = cnt[1];
+    if (cls != ROW_FAST) return false;
+    return !r64_needs_cyclic(r[0]) && !r64_needs_cyclic(r[1]);
+}
+
 }  // namespace acx

@@ -227,6 +227,7 @@ def gpu_arm(args):
     for b in range(N_BATCHES):
         states = walk_states_gpu(pool, n, seed=100 * rank + b, dev=dev)
         bufs.append(batch.EnvBuffers(states, HORIZON, pool=pool))
+        assert bufs[-1].certified, "bench states must be certified rows"
         bufs[-1].steps.copy_(torch.randint(0, HORIZON, (n,), device=dev, generator=g, dtype=torch.int32))
         acts.append(torch.randint(0, 12, (n,), device=dev, generator=g, dtype=torch.int64).to(torch.uint8))
         nxts.append(torch.randint(0, pool.shape[0], (n,), device=dev, generator=g, dtype=torch.int32))
@@ -269,7 +270,7 @@ def gpu_arm(args):
     env = vecenv.VecACEnv(pool_np, horizon_length=HORIZON, num_envs=n, device=str(dev),
                           start_index=np.random.default_rng(rank).integers(0, len(pool_np), n))
     env.reset()
-    env.buf.state.copy_(bufs[1].state)
+    env.buf.set_state(bufs[1].state)
     host_actions = [np.random.default_rng(7 + i).integers(0, 12, n).astype(np.int64) for i in range(4)]
     e2e_steps = max(3, min(args.steps, 20))
     for i in range(3):

@@ -80,10 +80,21 @@ int acx_rows_primitive(const int8_t* states_in, const uint8_t* moves, int8_t* st
  *     int32 reward | uint8 done | uint8 truncated | uint8 len(r_0) | uint8 len(r_1)
  * (lengths are those of the state left in `state`, i.e. after a reset if one happened).
  * reward_clipped (optional, float [n]) = clip(reward, clip_lo, clip_hi), the TransformReward
- * wrapper of agents/environment.py:48-52.  row_status [n] may be NULL. */
+ * wrapper of agents/environment.py:48-52.  row_status [n] may be NULL.
+ * flags: ACX_ENV_CERTIFIED promises that every row of `state` and of `pool` is certified
+ * (acx_rows_certify said so, or the row is the output of an earlier acx_env_step on certified rows)
+ * and that step_out[e].len0/len1 hold the current lengths of env e (acx_rows_certify writes them);
+ * the kernel then skips the per-row input checks.  Results are identical either way. */
+#define ACX_ENV_CERTIFIED 1
 int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
                  const int32_t* next_idx, uint8_t* step_out, float* reward_clipped, uint8_t* row_status,
-                 int64_t n, int m, int horizon, float clip_lo, float clip_hi, acx_stream_t stream);
+                 int64_t n, int m, int horizon, float clip_lo, float clip_hi, int flags, acx_stream_t stream);
+
+/* Row certification for the env fast path: certified_out[r] = 1 iff row r has letters in {0,+-1,+-2},
+ * zeros only as right padding, and both relators freely and cyclically reduced (every output of
+ * ACMove(cyclical=True) is).  lens_out [n,2] = relator lengths.  Either output may be NULL. */
+int acx_rows_certify(const int8_t* rows, int64_t n, int m, uint8_t* lens_out, uint8_t* certified_out,
+                     acx_stream_t stream);
 
 /* All 12 successors of every parent in one launch -- the `for action in range(12)` loops of
  * ac_solver/search/greedy.py:76-83 and ac_solver/search/breadth_first.py:69-76.

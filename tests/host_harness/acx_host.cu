@@ -48,10 +48,35 @@ static void run64(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* 
     }
 }
 
+// certified-row path (m == 36): rows that are not certified go through the checked path, as the
+// env kernel does per launch
+static void run_cert36(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status, int64_t n) {
+    const int m = 36, rowb = 72;
+    std::vector<uint64_t> a(rowb / 8 + 2);
+    for (int64_t r = 0; r < n; ++r) {
+        uint8_t* ia = reinterpret_cast<uint8_t*>(a.data());
+        memcpy(ia, in + r * rowb, rowb);
+        int l0 = -1, l1 = -1;
+        uint32_t st = 99;
+        if (row_is_certified(ia, m, l0, l1)) st = acmove_row64_certified<36>(ia, moves[r], l0, l1);
+        else acmove_row64<36>(ia, m, moves[r], true, l0, l1, st);
+        memcpy(out + r * rowb, ia, rowb);
+        lens[2 * r] = (uint8_t)l0;
+        lens[2 * r + 1] = (uint8_t)l1;
+        status[r] = (uint8_t)st;
+    }
+}
+
 // variant: 0 = dynamic width (generic planes), 1 = static generic planes (m must be 36 or 128),
-//          2 = 64-bit planes dynamic (m <= 64), 3 = 64-bit planes static (m == 36)
+//          2 = 64-bit planes dynamic (m <= 64), 3 = 64-bit planes static (m == 36),
+//          4 = certified-row env path (m == 36, cyclical only)
 extern "C" int acxh_move_batch(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status,
                                int64_t n, int m, int cyc, int variant, int inplace) {
+    if (variant == 4) {
+        if (m != 36 || !cyc) return -1;
+        run_cert36(in, moves, out, lens, status, n);
+        return 0;
+    }
     if (variant == 2) {
         if (m > 64) return -1;
         run64<0>(in, moves, out, lens, status, n, m, cyc);

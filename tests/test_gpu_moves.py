@@ -112,8 +112,7 @@ def test_env_step_golden(cuda, golden_dir):
             assert np.array_equal(buf.truncated.cpu().numpy(), g["truncated"][t, sel])
             assert np.array_equal(buf.lens.cpu().numpy(), g["lens"][t, sel])
             assert (buf.status.cpu().numpy() == 0).all()
-            buf.state.copy_(snap[0])
-            buf.steps.copy_(snap[1])
+            buf.set_state(snap[0], snap[1])
             batch.env_step(buf, _t(actions[t, sel], cuda), next_idx=idx)  # fused reset of finished envs
             fin = (g["done"][t, sel] | g["truncated"][t, sel]).astype(bool)
             exp = g["obs"][t, sel].copy()
@@ -165,3 +164,38 @@ def test_expand12_vs_oracle(cuda, oracle, m, f):
         assert np.array_equal(ch.cpu().numpy(), ec)
         assert np.array_equal(l.cpu().numpy().astype(np.int32), el)
         assert np.array_equal(st.cpu().numpy(), es)
+
+
+def test_env_step_certified_vs_checked(cuda, oracle, golden_dir):
+    """the certified-row kernel and the checked kernel give identical trajectories (and match the oracle);
+    an uncertifiable pool row switches the buffers to the checked kernel"""
+    import torch
+    from acx import batch
+
+    m, horizon, n = 36, 25, 40000
+    roots = dataset_rows(golden_dir)
+    pool = np.stack([repad(r, m) for r in roots[:300]])
+    states = walk_states(oracle, roots, m, 4096, 30, seed=11, cyclical=True)
+    rng = np.random.default_rng(2)
+    state = states[rng.integers(0, len(states), n)].copy()
+    steps = np.zeros(n, dtype=np.int32)
+    a = batch.EnvBuffers(_t(state, cuda), horizon=horizon, pool=_t(pool, cuda))
+    b = batch.EnvBuffers(_t(state, cuda), horizon=horizon, pool=_t(pool, cuda))
+    assert a.certified and b.certified
+    b.certified = False  # force the checked kernel
+    for t in range(60):
+        act = rng.integers(0, 12, n).astype(np.uint8)
+        nxt = rng.integers(0, len(pool), n).astype(np.int32)
+        rew, done, trunc, lens, st = oracle.env_step_batch(state, steps, act, horizon, pool=pool, next_idx=nxt, threads=8)
+        for buf in (a, b):
+            batch.env_step(buf, _t(act, cuda), next_idx=_t(nxt, cuda))
+            assert np.array_equal(buf.state.cpu().numpy(), state)
+            assert np.array_equal(buf.step_out.cpu().numpy()[:, :4].copy().view(np.int32)[:, 0], rew)
+            assert np.array_equal(buf.done.cpu().numpy(), done)
+            assert np.array_equal(buf.truncated.cpu().numpy(), trunc)
+            assert np.array_equal(buf.lens.cpu().numpy(), lens)
+            assert np.array_equal(buf.steps.cpu().numpy(), steps)
+    bad_pool = pool.copy()
+    bad_pool[5, :4] = [1, 2, -2, 1]  # not freely reduced
+    c = batch.EnvBuffers(_t(state, cuda), horizon=horizon, pool=_t(bad_pool, cuda))
+    assert not c.certified

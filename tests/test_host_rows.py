@@ -48,3 +48,26 @@ def test_host_rows_fuzz(oracle, m):
             assert np.array_equal(o, eo)
             assert np.array_equal(l.astype(np.int32), el)
             assert np.array_equal(st, es)
+
+
+def test_host_certified_rows(oracle, golden_dir):
+    """the certified-row fast path of the env kernel (rotation conjugation, 2-plane pack) on AC-walk
+    states and on the reduced golden rows; uncertified rows fall back to the checked path"""
+    from helpers import dataset_rows, walk_states
+
+    roots = dataset_rows(golden_dir)
+    states = walk_states(oracle, roots, 36, 6000, 40, seed=5, cyclical=True)
+    rng = np.random.default_rng(9)
+    # short relators (length 1..3) exercise the rotation edge cases
+    short = random_rows(rng, 3000, 36, kinds=(1,))
+    short[:, 3:36] = 0
+    short[:, 36 + 2:] = 0
+    mixed = random_rows(rng, 3000, 36)
+    rows = np.concatenate([states, short, mixed])
+    for rep in range(3):
+        mv = rng.integers(0, 12, len(rows)).astype(np.uint8)
+        eo, el, es = oracle.acmove_batch(rows, mv, cyclical=1, threads=4)
+        o, l, st = harness.move_batch(rows, mv, 1, 4, 1)
+        assert np.array_equal(o, eo)
+        assert np.array_equal(l.astype(np.int32), el)
+        assert np.array_equal(st, es)
