@@ -125,10 +125,10 @@ __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t nti
         }
     }
 
-    int it = 0;
-    for (int64_t t = first; t < ntiles; t += stride, ++it) {
-        const int s = it % S;
-        const uint32_t parity = (uint32_t)(it / S) & 1u;
+    uint32_t s = 0, parity = 0, sprev = S - 1;  // stage of this iteration / its mbarrier phase / previous stage
+    bool first_it = true;
+    uint8_t* const my_rows = smem + (uint32_t)tid * ROWB;
+    for (int64_t t = first; t < ntiles; t += stride) {
         const int64_t row = p.row0 + t * TR + tid;
         const int move = p.actions[row];
         int32_t steps_in = 0;
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t nti
         }
         mbar_wait(bar0 + 8 * s, parity);
 
-        uint8_t* srow = smem + (size_t)s * TILEB + (size_t)tid * ROWB;
+        uint8_t* srow = my_rows + s * TILEB;
         uint32_t status;
         if constexpr (CERT) status = acmove_row64_certified<MS>(srow, move, l0, l1);
         else row_move<W, MS>(srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
@@ -152,15 +152,20 @@ __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t nti
         if (tid == 0) {
             bulk_store(gout + t * TILEB, smem0 + s * TILEB, TILEB);
             bulk_commit();
-            if (it >= 1) {  // refill the stage whose store was issued one iteration ago
+            if (!first_it) {  // refill the stage whose store was issued one iteration ago
                 bulk_wait_read<1>();
-                const int sp = (it - 1) % S;
                 const int64_t tn = t + (int64_t)(S - 1) * stride;
                 if (tn < ntiles) {
-                    mbar_expect_tx(bar0 + 8 * sp, TILEB);
-                    bulk_load(smem0 + sp * TILEB, gin + tn * TILEB, TILEB, bar0 + 8 * sp);
+                    mbar_expect_tx(bar0 + 8 * sprev, TILEB);
+                    bulk_load(smem0 + sprev * TILEB, gin + tn * TILEB, TILEB, bar0 + 8 * sprev);
                 }
             }
+        }
+        first_it = false;
+        sprev = s;
+        if (++s == S) {
+            s = 0;
+            parity ^= 1u;
         }
     }
     if (tid == 0) bulk_wait_all<0>();
@@ -330,12 +335,25 @@ static int tma_stages() {  // ACX_STAGES=3|4 (tuning knob; default 3)
     return v;
 }
 
+static int tile_rows() {  // ACX_TILE=64|128|256 (tuning knob; default 128)
+    static int v = 0;
+    if (v == 0) {
+        const char* e = getenv("ACX_TILE");
+        v = e ? atoi(e) : 128;
+        if (v != 64 && v != 256) v = 128;
+    }
+    return v;
+}
+
 template <bool ENV>
 static int run_rows(StepParams p, cudaStream_t st) {
     if (p.n == 0) return ACX_OK;
     p.row0 = 0;
     switch (p.m) {
-        case 36: return tma_stages() == 3 ? run_static<2, 36, 128, 3, ENV>(p, st) : run_static<2, 36, 128, 4, ENV>(p, st);
+        case 36:
+            if (tile_rows() == 256) return run_static<2, 36, 256, 3, ENV>(p, st);
+            if (tile_rows() == 64) return run_static<2, 36, 64, 4, ENV>(p, st);
+            return tma_stages() == 3 ? run_static<2, 36, 128, 3, ENV>(p, st) : run_static<2, 36, 128, 4, ENV>(p, st);
         case 128: return run_static<4, 128, 64, 4, ENV>(p, st);
         default: break;
     }

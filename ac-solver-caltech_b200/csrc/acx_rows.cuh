@@ -484,8 +484,8 @@ ACX_HD void acmove_row64(uint8_t* row, int m_rt, int move, bool cyc, int& l0, in
             o_changed = true;
         }
     }
-    uint8_t* pa = row + (i ? m : 0);
-    uint8_t* po = row + (i ? 0 : m);
+    uint8_t* pa = row + (d & 1u) * m;
+    uint8_t* po = row + ((d & 1u) ^ 1u) * m;
     if (a_changed) {
         if (MS) unpack_rel_static64<(MS ? MS : 4)>(pa, a);
         else unpack_rel_dynamic64(pa, m, a);
@@ -572,7 +572,7 @@ ACX_HD uint32_t acmove_row64_certified(uint8_t* row, int move, int& l0, int& l1)
             a.T = ((a.T << 1) & mk) | (uint64_t)tl;
         }
     }
-    if (changed) unpack_rel_static64<MS>(row + (i ? MS : 0), a);
+    if (changed) unpack_rel_static64<MS>(row + (d & 1u) * MS, a);  // one copy of the code, address by arithmetic
     l0 = i ? o.n : a.n;
     l1 = i ? a.n : o.n;
     return ACX_ROW_OK;

@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--impl", default="acx", choices=["acx", "reference"])
     ap.add_argument("--envs", type=int, default=N_ENV)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of one CUDA graph")
     return ap.parse_args()
 
 
@@ -249,9 +250,24 @@ def gpu_arm(args):
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_wall0 = time.time()
+    graph = None
+    if not args.no_graph:  # the K timed launches as ONE CUDA graph (same kernels, same order, same buffers)
+        graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(graph, stream=side):
+                for k in range(args.steps):
+                    step(args.warmup + k)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        barrier()
+        t_wall0 = time.time()
     e0.record()
-    for k in range(args.steps):
-        step(args.warmup + k)
+    if graph is not None:
+        graph.replay()
+    else:
+        for k in range(args.steps):
+            step(args.warmup + k)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -309,7 +325,7 @@ def gpu_arm(args):
         "e2e": {"value": world * n * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": env.h2d_bytes_per_step, "d2h_bytes_per_step": env.d2h_bytes_per_step,
                 "api": "acx.vecenv.VecACEnv.step(numpy actions) -> numpy obs/reward/done/truncated", "steps": e2e_steps},
-        "gpu_launches": args.steps,
+        "gpu_launches": args.steps, "launch_mode": "python loop" if args.no_graph else "one CUDA graph of the K launches",
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "kernel": "k_rows_tma<2,36,128,4,ENV>",
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
