@@ -14,6 +14,7 @@
 #include "../../include/acx.h"
 #include "acx_common.h"
 #include "acx_rows.cuh"
+#include "acx_expand_warp.cuh"
 
 namespace acx {
 
@@ -96,6 +97,147 @@ static int launch_expand_simple(const ExpandParams& p, cudaStream_t st) {
     return ACX_OK;
 }
 
+template <int VEC>
+struct VecT;
+template <>
+struct VecT<8> {
+    using T = uint2;
+};
+template <>
+struct VecT<16> {
+    using T = uint4;
+};
+
+// one thread per parent; see acx_expand_warp.cuh
+template <int W, int MS, int GM, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) k_expand_warp(const ExpandParams p, int64_t ntiles) {
+    using Ops = PlaneOps<W, MS>;
+    using R = typename Ops::R;
+    constexpr int ROWB = 2 * MS;
+    constexpr int VEC = (ROWB % 16 == 0) ? 16 : 8;
+    using V = typename VecT<VEC>::T;
+    constexpr int PSTRIDE = (ROWB % 128 == 0) ? ROWB + 16 : ROWB;  // padded against bank conflicts
+    constexpr int CSTRIDE = GM * ROWB + VEC;
+    constexpr int WARP_BYTES = 32 * (2 * PSTRIDE + CSTRIDE);
+    constexpr int PCH = ROWB / VEC, CCH = GM * ROWB / VEC;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint8_t* par = smem + (size_t)wid * WARP_BYTES;
+    uint8_t* base = par + 32 * PSTRIDE;
+    uint8_t* cbuf = base + 32 * PSTRIDE;
+    const bool cyc = p.cyclical != 0;
+    const int64_t warp0 = (int64_t)blockIdx.x * WARPS + wid, nwarps = (int64_t)gridDim.x * WARPS;
+    const uint8_t* gpar = reinterpret_cast<const uint8_t*>(p.parents);
+    uint8_t* gch = reinterpret_cast<uint8_t*>(p.children);
+
+    for (int64_t tile = warp0; tile < ntiles; tile += nwarps) {
+        const int64_t f0 = tile * 32;
+        const int nrows = (int)min((int64_t)32, p.f - f0);
+        for (int c = lane; c < nrows * PCH; c += 32) {
+            const int pr = c / PCH, o = c - pr * PCH;
+            *reinterpret_cast<V*>(par + pr * PSTRIDE + o * VEC) = *reinterpret_cast<const V*>(gpar + f0 * ROWB + (size_t)c * VEC);
+        }
+        __syncwarp();
+        const bool active = lane < nrows;
+        uint8_t* prow = par + lane * PSTRIDE;
+        uint8_t* brow = base + lane * PSTRIDE;
+        R r[2], rc[2];
+        int cnt[2] = {0, 0};
+        int cls = ROW_INVALID;
+        if (active) cls = Ops::classify(prow, r, cnt);
+        const bool fast = active && cls == ROW_FAST;
+        if (fast) {  // base row = the parent with both relators simplified (utils.py:270-281)
+            for (int k = 0; k < PCH; ++k) reinterpret_cast<V*>(brow)[k] = reinterpret_cast<const V*>(prow)[k];
+            rc[0] = r[0];
+            rc[1] = r[1];
+            if (cyc) {
+                Ops::cyclic(rc[0]);
+                Ops::cyclic(rc[1]);
+                if (rc[0].n != r[0].n) Ops::unpack(brow, rc[0]);
+                if (rc[1].n != r[1].n) Ops::unpack(brow + MS, rc[1]);
+            }
+        }
+#pragma unroll 1
+        for (int g = 0; g < 12 / GM; ++g) {
+#pragma unroll 1
+            for (int j = 0; j < GM; ++j) {
+                const int a = g * GM + j;
+                uint8_t* child = cbuf + lane * CSTRIDE + j * ROWB;
+                if (!active) continue;
+                int l0 = cnt[0], l1 = cnt[1];
+                uint32_t st = ACX_ROW_OK;
+                if (fast) {
+                    const uint32_t d = decode_move(a);
+                    const bool i = d & 1u, is_conj = d & 2u, inv = d & 4u;
+                    R x = Ops::select(i, r[0], r[1]);
+                    bool changed;
+                    if (!is_conj) {
+                        R b = Ops::select(!i, r[0], r[1]);
+                        if (inv) b = Ops::inverse(b);
+                        changed = Ops::concat(x, b);
+                    } else {
+                        changed = Ops::conjugate(x, inv ? 1u : 0u, (d >> 3) & 1u);
+                    }
+                    if (x.n == 0) {  // utils.py:264-266 raises: the child slot holds the parent unchanged
+                        st = ACX_ROW_EMPTY_RELATOR;
+                        for (int k = 0; k < PCH; ++k) reinterpret_cast<V*>(child)[k] = reinterpret_cast<const V*>(prow)[k];
+                    } else {
+                        for (int k = 0; k < PCH; ++k) reinterpret_cast<V*>(child)[k] = reinterpret_cast<const V*>(brow)[k];
+                        if (changed) {
+                            if (cyc) Ops::cyclic(x);
+                            Ops::unpack(child + (d & 1u) * MS, x);
+                        }
+                        const int na = changed ? x.n : (i ? rc[1].n : rc[0].n);
+                        l0 = i ? rc[0].n : na;
+                        l1 = i ? na : rc[1].n;
+                    }
+                } else {  // rows outside the plane domain: the checked row function on a copy of the parent
+                    for (int k = 0; k < PCH; ++k) reinterpret_cast<V*>(child)[k] = reinterpret_cast<const V*>(prow)[k];
+                    if constexpr (W <= 2) acmove_row64<MS>(child, MS, a, cyc, l0, l1, st);
+                    else acmove_row<W, MS>(child, child, MS, a, cyc, l0, l1, st);
+                }
+                const int64_t c = (f0 + lane) * 12 + a;
+                if (p.lens) *reinterpret_cast<uchar2*>(p.lens + 2 * c) = make_uchar2((uint8_t)l0, (uint8_t)l1);
+                if (p.status) p.status[c] = (uint8_t)st;
+            }
+            __syncwarp();
+            uint8_t* gdst = gch + (f0 * 12 + (int64_t)g * GM) * ROWB;
+            for (int c = lane; c < nrows * CCH; c += 32) {
+                const int pr = c / CCH, o = c - pr * CCH;
+                *reinterpret_cast<V*>(gdst + (size_t)pr * 12 * ROWB + o * VEC) =
+                    *reinterpret_cast<const V*>(cbuf + pr * CSTRIDE + o * VEC);
+            }
+            __syncwarp();
+        }
+    }
+}
+
+template <int W, int MS, int GM, int WARPS>
+static int launch_expand_warp(const ExpandParams& p, cudaStream_t st) {
+    constexpr int ROWB = 2 * MS;
+    constexpr int VEC = (ROWB % 16 == 0) ? 16 : 8;
+    constexpr int PSTRIDE = (ROWB % 128 == 0) ? ROWB + 16 : ROWB;
+    constexpr int CSTRIDE = GM * ROWB + VEC;
+    constexpr size_t smem = (size_t)WARPS * 32 * (2 * PSTRIDE + CSTRIDE);
+    auto kern = k_expand_warp<W, MS, GM, WARPS>;
+    static int ctas_per_sm[ACX_MAX_DEVICES] = {0};
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= ACX_MAX_DEVICES) dev = 0;
+    if (ctas_per_sm[dev] == 0) {
+        ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 0;
+        ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * WARPS, smem));
+        ctas_per_sm[dev] = occ > 0 ? occ : 1;
+    }
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t ntiles = (p.f + 31) / 32;
+    const int64_t grid = std::min<int64_t>((ntiles + WARPS - 1) / WARPS, (int64_t)sms * ctas_per_sm[dev]);
+    kern<<<(unsigned)grid, 32 * WARPS, smem, st>>>(p, ntiles);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
 }  // namespace acx
 
 using namespace acx;
@@ -114,6 +256,9 @@ extern "C" int acx_expand12(const int8_t* parents, int8_t* children, uint8_t* ch
     p.m = m;
     p.cyclical = cyclical;
     cudaStream_t st = (cudaStream_t)stream;
+    const bool aligned = (((uintptr_t)parents | (uintptr_t)children) & 15u) == 0;
+    if (aligned && m == 36) return launch_expand_warp<2, 36, 4, 4>(p, st);
+    if (aligned && m == 128) return launch_expand_warp<4, 128, 1, 4>(p, st);
     if (m <= 32) return launch_expand_simple<1, 8>(p, st);
     if (m <= 64) return launch_expand_simple<2, 8>(p, st);
     return launch_expand_simple<4, 8>(p, st);

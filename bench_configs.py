@@ -1,0 +1,173 @@
+#!/usr/bin/env python
+"""bench_configs.py -- the other BASELINE.json configs (bench.py measures configs[1]).
+
+    python bench_configs.py [greedy] [expand] [ppo] [bfs]
+
+Prints one JSON line per config.  Same timing rules as bench.py (CUDA events, warm-up, footprint > L2)."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "ac-solver-caltech_b200"))
+sys.path.insert(0, ROOT)
+import bench as B  # noqa: E402
+from acx import batch, search  # noqa: E402
+
+PEAK = 6538.3
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except OSError:
+    pass
+
+
+def dataset_rows():
+    z = np.load(os.path.join(ROOT, "tests", "golden", "dataset.npz"))
+    widths, flat = z["widths"], z["flat"]
+    off = np.concatenate([[0], np.cumsum(widths)])
+    return [flat[off[k]:off[k + 1]].copy() for k in range(len(widths))]
+
+
+def cfg_greedy(dev):
+    """configs[0]: greedy_search over the 1190 Miller-Schupp presentations, max_nodes_to_explore=10000."""
+    rows = dataset_rows()
+    by_width = {}
+    for k, r in enumerate(rows):
+        by_width.setdefault(len(r), []).append(k)
+    groups = [np.stack([rows[k] for k in idx]) for idx in by_width.values()]
+    for rep in range(2):  # first pass warms up
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        solved = expanded = 0
+        for g in groups:
+            res, _ = search.search_batch(g, 10000, False, True, str(dev))
+            solved += int(res[:, search.RES_SOLVED].sum())
+            expanded += int(res[:, search.RES_EXPANDED].sum())
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    return {"config": "configs[0] greedy_search x 1190 presentations @ max_nodes_to_explore=10000", "solved": solved,
+            "wall_s": dt, "nodes_expanded": expanded, "nodes_expanded_per_s": expanded / dt,
+            "ac_moves_per_s": 12 * expanded / dt,
+            "reference": "1356.8 s on one core, 380 solved (SURVEY.md section 6)", "includes": "H2D of roots, D2H of results/paths"}
+
+
+def cfg_expand(dev, m=128, chunk=1 << 19, total=10 ** 8):
+    """configs[4]: full 12-move neighbourhood expansion of a 1e8-state frontier, max_relator_length=128,
+    streamed through HBM in chunks (children of one chunk: chunk*12*2m bytes)."""
+    pool = torch.from_numpy(np.stack([np.concatenate([r[:len(r) // 2][r[:len(r) // 2] != 0],
+                                                       np.zeros(m, np.int8)])[:m].tolist() +
+                                      np.concatenate([r[len(r) // 2:][r[len(r) // 2:] != 0],
+                                                      np.zeros(m, np.int8)])[:m].tolist()
+                                      for r in dataset_rows()]).astype(np.int8)).to(dev)
+    g = torch.Generator(device=dev)
+    g.manual_seed(2)
+    nb = 3  # rotating parent chunks; the children buffers alone (chunk*12*2m) exceed L2 many times over
+    parents = []
+    for b in range(nb):
+        states = pool[torch.randint(0, pool.shape[0], (chunk,), device=dev, generator=g)].contiguous()
+        walk = torch.randint(0, 257, (chunk,), device=dev, generator=g)
+        for t in range(256):
+            mv = torch.randint(0, 12, (chunk,), device=dev, generator=g, dtype=torch.int64).to(torch.uint8)
+            nxt, _, st = batch.move_batch(states, mv, cyclical=False)
+            states = torch.where(((walk > t) & (st == 0))[:, None], nxt, states)
+        parents.append(states.contiguous())
+    n_chunks = (total + chunk - 1) // chunk
+    for b in range(nb):
+        batch.expand12(parents[b], cyclical=False)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    outs = [batch.expand12(parents[0], cyclical=False), batch.expand12(parents[1], cyclical=False)]
+    import ctypes
+    from acx import _lib
+    L = _lib.lib()
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    torch.cuda.synchronize()
+    e0.record()
+    for k in range(n_chunks):
+        ch, ln, st = outs[k % 2]
+        L.acx_expand12(parents[k % nb].data_ptr(), ch.data_ptr(), ln.data_ptr(), st.data_ptr(), chunk, m, 0, stream)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    done = n_chunks * chunk
+    alg = 26 * m + 24 + 12  # read 2m, write 12*(2m+2) (+12 status bytes)
+    lens_mean = float(parents[0].ne(0).sum(dim=1).float().mean().item())
+    return {"config": "configs[4] 12-move expansion of a 1e8-state frontier, max_relator_length=%d" % m,
+            "parents": done, "chunk": chunk, "ms_total": ms, "parents_per_s": done / (ms * 1e-3),
+            "transitions_per_s": 12 * done / (ms * 1e-3), "alg_bytes_per_parent": alg,
+            "roofline": {"bound": "hbm", "achieved": done * alg / (ms * 1e-3) / 1e9, "peak": PEAK, "unit": "GB/s",
+                         "frac": done * alg / (ms * 1e-3) / 1e9 / PEAK},
+            "mean_total_length_of_parents": lens_mean}
+
+
+def cfg_ppo(dev, n=65536, T=64):
+    """configs[2]: PPO rollout with 65,536 GPU-resident envs: the reference Agent's 2x256 tanh MLP samples the
+    actions on the same GPU (agents/ppo_agent.py:52-109), no host hop per step."""
+    from acx import vecenv
+
+    pool = B.load_pool()
+    env = vecenv.VecACEnv(pool, horizon_length=2000, num_envs=n, device=str(dev))
+    env.reset()
+    torch.manual_seed(0)
+    actor = torch.nn.Sequential(torch.nn.Linear(72, 256), torch.nn.Tanh(), torch.nn.Linear(256, 256), torch.nn.Tanh(),
+                                torch.nn.Linear(256, 12)).to(dev)
+    critic = torch.nn.Sequential(torch.nn.Linear(72, 256), torch.nn.Tanh(), torch.nn.Linear(256, 256), torch.nn.Tanh(),
+                                 torch.nn.Linear(256, 1)).to(dev)
+    obs_buf = torch.zeros((T, n, 72), dtype=torch.int8, device=dev)
+    act_buf = torch.zeros((T, n), dtype=torch.uint8, device=dev)
+    rew_buf = torch.zeros((T, n), dtype=torch.float32, device=dev)
+    done_buf = torch.zeros((T, n), dtype=torch.uint8, device=dev)
+    val_buf = torch.zeros((T, n), dtype=torch.float32, device=dev)
+
+    def rollout(with_policy):
+        for t in range(T):
+            obs = env.buf.state
+            obs_buf[t].copy_(obs)
+            if with_policy:
+                with torch.no_grad():
+                    x = obs.float()
+                    logits = actor(x)
+                    val_buf[t].copy_(critic(x).squeeze(-1))
+                    a = torch.distributions.Categorical(logits=logits).sample().to(torch.uint8)
+            else:
+                a = act_buf[(t + 1) % T]
+            act_buf[t].copy_(a)
+            _, r, d, tr = env.step_device(act_buf[t])
+            rew_buf[t].copy_(r)
+            done_buf[t].copy_(d | tr)
+
+    out = {}
+    for with_policy in (True, False):
+        rollout(with_policy)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            rollout(with_policy)
+        e1.record()
+        torch.cuda.synchronize()
+        out["env_steps_per_s_%s" % ("with_policy" if with_policy else "env_only")] = 3 * T * n / (e0.elapsed_time(e1) * 1e-3)
+    out.update({"config": "configs[2] PPO rollout, %d GPU-resident envs per B200, %d steps per rollout" % (n, T),
+                "reference": "627 env-steps/s end to end with 4 envs (experiments/results/2026-02-23_03-11-29_ppo_rnd/results.json)"})
+    return out
+
+
+if __name__ == "__main__":
+    dev = torch.device("cuda:0")
+    which = sys.argv[1:] or ["greedy", "expand", "ppo"]
+    for w in which:
+        if w == "greedy":
+            print(json.dumps(cfg_greedy(dev)))
+        elif w == "expand":
+            print(json.dumps(cfg_expand(dev)))
+        elif w == "expand36":
+            print(json.dumps(cfg_expand(dev, m=36, chunk=1 << 20, total=1 << 26)))
+        elif w == "ppo":
+            print(json.dumps(cfg_ppo(dev)))
+        elif w == "bfs":
+            import bench_bfs
+            print(json.dumps(bench_bfs.run(dev)))
