@@ -117,6 +117,28 @@ int acx_search_batch(const int8_t* roots, int n_instances, int m, int64_t budget
                      void* workspace, int64_t workspace_bytes, int32_t* result, int32_t* path, int path_cap,
                      acx_stream_t stream);
 
+/* Level-synchronous bfs building blocks (ac_solver/search/breadth_first.py:15-97 for frontiers too large
+ * for one warp; driver: acx/bfs.py, sharded driver: acx/bfs_sharded.py).  m must be even.
+ * The visited table is an open-addressing array of tcap (power of two) 64-bit slots, zero = empty.
+ *   acx_bfs_seed    puts the root (node `node_id`) into the table.
+ *   acx_bfs_probe   for the n candidate rows of one round (children of the frontier in discovery order,
+ *                   candidate j = parent_rank*12 + action, or order[j] when given): slot_out[j] = its slot,
+ *                   -1 = already visited, -2 = not inserted (total length 2 -> *min_success = min order;
+ *                   non-zero status -> *min_error = min order); is_new_out[j] = 1 iff j is the first
+ *                   candidate (smallest order) carrying a state that was not visited before;
+ *                   hash_out (optional) = the 64-bit row hash (the owner key of the sharded bfs).
+ *   acx_bfs_commit  turns the new candidates j < limit into nodes node_base + new_rank[j] (new_rank =
+ *                   exclusive scan of is_new), recording parent id, action and total length. */
+int acx_bfs_seed(const int8_t* row, int m, uint64_t* table, int64_t tcap, int64_t node_id, acx_stream_t stream);
+int acx_bfs_probe(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* order, int64_t n,
+                  int m, uint64_t* table, int64_t tcap, const int8_t* nodes, int64_t* slot_out,
+                  uint64_t* min_success, uint64_t* min_error, uint64_t* hash_out, uint8_t* is_new_out,
+                  acx_stream_t stream);
+int acx_bfs_commit(const int8_t* cand, const uint8_t* lens, const int64_t* slot, const uint8_t* is_new,
+                   const int64_t* new_rank, const int64_t* parent_id, int64_t parent_base, int64_t n, int64_t limit,
+                   int m, uint64_t* table, int8_t* nodes, int64_t* parent, uint8_t* action, uint16_t* total,
+                   int64_t node_base, acx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
