@@ -145,7 +145,7 @@ struct CommitParams {
     const int64_t* slot;
     const uint8_t* is_new;
     const int64_t* new_rank;  // [n] exclusive scan of is_new
-    const int64_t* parent_id; // [n / 12] node id (global) of each parent, or null (= parent_base + j / 12)
+    const int64_t* order;     // [n] discovery number of each candidate relative to parent_base*12, or null (= j)
     int64_t parent_base;
     int64_t n, limit;         // only candidates j < limit are committed
     int rowb;
@@ -169,11 +169,18 @@ __global__ void k_bfs_commit(const CommitParams p) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(p.cand + j * p.rowb);
     uint32_t* dst = reinterpret_cast<uint32_t*>(p.nodes + id * p.rowb);
     for (int k = 0; k < nwords; ++k) dst[k] = src[k];
-    p.parent[id] = p.parent_id ? p.parent_id[j / 12] : (p.parent_base + j / 12);
-    p.action[id] = (uint8_t)(j % 12);
+    const int64_t ord = p.order ? p.order[j] : j;
+    p.parent[id] = p.parent_base + ord / 12;
+    p.action[id] = (uint8_t)(ord % 12);
     p.total[id] = (uint16_t)((int)p.lens[2 * j] + (int)p.lens[2 * j + 1]);
     const uint64_t e = p.table[s];
     p.table[s] = (e & ~(PROV_BIT | VAL_MASK)) | (uint64_t)id;
+}
+
+__global__ void k_rows_hash(const int8_t* rows, int64_t n, int rowb, uint64_t* out) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    out[j] = bfs_row_hash(reinterpret_cast<const uint32_t*>(rows + j * rowb), rowb / 4);
 }
 
 // root insertion
@@ -218,17 +225,26 @@ extern "C" int acx_bfs_probe(const int8_t* cand, const uint8_t* lens, const uint
 }
 
 extern "C" int acx_bfs_commit(const int8_t* cand, const uint8_t* lens, const int64_t* slot, const uint8_t* is_new,
-                              const int64_t* new_rank, const int64_t* parent_id, int64_t parent_base, int64_t n, int64_t limit,
+                              const int64_t* new_rank, const int64_t* order, int64_t parent_base, int64_t n, int64_t limit,
                               int m, uint64_t* table, int8_t* nodes, int64_t* parent, uint8_t* action, uint16_t* total,
                               int64_t node_base, acx_stream_t stream) {
     if (n < 0 || m < 1 || (2 * m) % 4 != 0) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit: bad argument");
     if (n == 0) return ACX_OK;
     if (!cand || !lens || !slot || !is_new || !new_rank || !table || !nodes || !parent || !action || !total) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit: null pointer");
     CommitParams p;
-    p.cand = cand; p.lens = lens; p.slot = slot; p.is_new = is_new; p.new_rank = new_rank; p.parent_id = parent_id;
+    p.cand = cand; p.lens = lens; p.slot = slot; p.is_new = is_new; p.new_rank = new_rank; p.order = order;
     p.parent_base = parent_base; p.n = n; p.limit = limit; p.rowb = 2 * m; p.table = table; p.nodes = nodes; p.parent = parent;
     p.action = action; p.total = total; p.node_base = node_base;
     k_bfs_commit<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+extern "C" int acx_rows_hash(const int8_t* rows, int64_t n, int m, uint64_t* hash_out, acx_stream_t stream) {
+    if (n < 0 || m < 1 || (2 * m) % 4 != 0) return acx_fail(ACX_ERR_ARG, "acx_rows_hash: bad argument (m must be even)");
+    if (n == 0) return ACX_OK;
+    if (!rows || !hash_out) return acx_fail(ACX_ERR_ARG, "acx_rows_hash: null pointer");
+    k_rows_hash<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rows, n, 2 * m, hash_out);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }

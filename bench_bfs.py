@@ -34,7 +34,45 @@ def run(dev, budget=10 ** 7, chunk=1 << 20):
             "reference": "660 expanded nodes/s, 5.6k discovered nodes/s at budget 1e5 (SURVEY.md section 6)"}
 
 
-if __name__ == "__main__":
+def run_sharded(budget=10 ** 8, chunk=1 << 20):
+    """torchrun entry: hash-partitioned bfs over WORLD_SIZE GPUs, strong scaling at a fixed budget."""
+    import torch.distributed as dist
+
+    from acx.bfs_sharded import GpuShard, ShardedBFS
+
+    world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    os.environ["NCCL_DEBUG"] = "WARN"
+    dist.init_process_group("nccl", device_id=dev)
+    out = None
+    for b in (10 ** 5, budget):  # first pass = warm-up (NCCL channels, kernels)
+        cap_local = int(b / world * 1.25) + 4096
+        max_cand = int(12 * chunk / world * 1.25) + 4096
+        shard = GpuShard(36, False, cap_local, max_cand, str(dev))
+        eng = ShardedBFS(ak3(), b, shard, chunk=chunk)
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ok, path = eng.run()
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        sent = torch.tensor([eng.comm_bytes], device=dev, dtype=torch.int64)
+        dist.all_reduce(sent)
+        out = {"config": "configs[3] hash-partitioned level-synchronous bfs from AK(3), m=36, budget %d" % b,
+               "n_gpus": world, "solved": ok, "n_seen": eng.n_nodes, "nodes_expanded": eng.n_expanded, "wall_s": float(dt[0]),
+               "nodes_expanded_per_s": eng.n_expanded / float(dt[0]), "all_to_all_bytes_total": int(sent[0]),
+               "scaling": "strong", "levels": eng.levels}
+    if rank == 0:
+        import json
+        print(json.dumps(out))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "sharded":
+    run_sharded(int(float(sys.argv[2])) if len(sys.argv) > 2 else 10 ** 8)
+elif __name__ == "__main__":
     import json
 
     b = int(float(sys.argv[1])) if len(sys.argv) > 1 else 10 ** 7

@@ -128,16 +128,19 @@ int acx_search_batch(const int8_t* roots, int n_instances, int m, int64_t budget
  *                   candidate (smallest order) carrying a state that was not visited before;
  *                   hash_out (optional) = the 64-bit row hash (the owner key of the sharded bfs).
  *   acx_bfs_commit  turns the new candidates j < limit into nodes node_base + new_rank[j] (new_rank =
- *                   exclusive scan of is_new), recording parent id, action and total length. */
+ *                   exclusive scan of is_new), recording parent id = parent_base + order/12, action =
+ *                   order % 12 (order[j] = j when order is NULL) and total length.
+ *   acx_rows_hash   the 64-bit state hash the table uses; the sharded bfs partitions states by it. */
 int acx_bfs_seed(const int8_t* row, int m, uint64_t* table, int64_t tcap, int64_t node_id, acx_stream_t stream);
 int acx_bfs_probe(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* order, int64_t n,
                   int m, uint64_t* table, int64_t tcap, const int8_t* nodes, int64_t* slot_out,
                   uint64_t* min_success, uint64_t* min_error, uint64_t* hash_out, uint8_t* is_new_out,
                   acx_stream_t stream);
 int acx_bfs_commit(const int8_t* cand, const uint8_t* lens, const int64_t* slot, const uint8_t* is_new,
-                   const int64_t* new_rank, const int64_t* parent_id, int64_t parent_base, int64_t n, int64_t limit,
+                   const int64_t* new_rank, const int64_t* order, int64_t parent_base, int64_t n, int64_t limit,
                    int m, uint64_t* table, int8_t* nodes, int64_t* parent, uint8_t* action, uint16_t* total,
                    int64_t node_base, acx_stream_t stream);
+int acx_rows_hash(const int8_t* rows, int64_t n, int m, uint64_t* hash_out, acx_stream_t stream);
 
 #ifdef __cplusplus
 }

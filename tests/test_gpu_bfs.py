@@ -52,3 +52,34 @@ def test_bfs_level_ak3_levels(cuda):
     ok, path = bfs_level(pad_row(AK3[0], AK3[1], 36), 100000, False, str(cuda), stats=stats)
     assert not ok and path is None
     assert stats["levels"][:6] == [1, 12, 116, 1045, 9142, 76612]
+
+
+def test_sharded_bfs_single_rank_gpu(cuda, oracle, golden_dir):
+    """the product shard backend (GpuShard: libacx kernels) under the sharded driver, world_size 1 (NCCL)"""
+    import torch
+    import torch.distributed as dist
+
+    from acx.bfs_sharded import GpuShard, ShardedBFS
+
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", str(29700 + os.getpid() % 200))
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=cuda)
+    try:
+        rows = dataset_rows(golden_dir)
+        rng = np.random.default_rng(21)
+        for k in rng.choice(len(rows), size=8, replace=False):
+            for budget, chunk in ((1, 4), (14, 4), (700, 64), (30000, 4096)):
+                cyc = bool(rng.integers(0, 2))
+                row = rows[int(k)]
+                shard = GpuShard(len(row) // 2, cyc, budget + 64, 12 * chunk, str(cuda))
+                eng = ShardedBFS(row, budget, shard, chunk=chunk)
+                ok, path = eng.run()
+                stats = {}
+                ook, opath = oracle.bfs(row, budget, False, cyc, stats=stats)
+                assert (ok, path) == (ook, opath), (int(k), budget, cyc)
+                assert eng.n_nodes == stats["n_seen"] and eng.n_expanded == stats["n_expanded"]
+    finally:
+        if created:
+            dist.destroy_process_group()
