@@ -4,16 +4,19 @@ Every state is owned by rank `owner(hash(state)) = (hash >> 20) % G`; a rank kee
 shard, the rows and the (parent, action, total) records of the states it owns.  Per round (a window of
 `chunk` frontier parents in GLOBAL discovery order):
 
-    expand local parents (acx_expand12)  ->  hash, bucket by owner  ->  all-to-all-v (NCCL over NVLink)
-    ->  insert into the local table shard with first-discovery semantics (acx_bfs_probe, order numbers
-        travel with the rows)  ->  all-reduce of one 12-bit "new" mask per parent (SUM == OR: bits are
-        disjoint)  ->  every rank derives the same global discovery ids, the same budget cut
-        (breadth_first.py:91-95) and the same early exit (:84-85)  ->  commit (acx_bfs_commit).
+    expand local parents (acx_expand12)  ->  hash, bucket by owner into packed records (acx_bfs_bucket)
+    ->  all-to-all-v (NCCL over NVLink)  ->  insert into the local table shard with first-discovery
+        semantics (acx_bfs_probe_packed: order numbers travel with the rows)  ->  all-reduce of one 12-bit
+        "new" mask per parent (SUM == OR: bits are disjoint)  ->  every rank derives the same global
+        discovery ids, the same budget cut (breadth_first.py:91-95) and the same early exit (:84-85)
+    ->  commit (acx_bfs_commit_packed).
 
 Global node ids therefore equal the reference's FIFO discovery order, and (solved, path, len(tree_nodes))
 are identical to the single-GPU engine and to the reference.  Host logic is plain torch + torch.distributed
 and is device agnostic: tests/ drive it on CPU with gloo and a stand-in shard backend; the product backend
 is GpuShard below (libacx kernels only, no CPU path)."""
+import time
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -37,29 +40,20 @@ def owner_of(h, world):
     return ((h >> 20) & 0x7FFFFFFF) % world
 
 
-def exchange(rows, order, lens, status, own, world, group=None):
-    """all-to-all-v of candidate records to their owners.  One record = row | order (8) | lens (2) | status (1),
-    padded to a multiple of 8 bytes; ONE payload collective per round (plus the count exchange)."""
-    n, rowb = rows.shape
-    rec = (rowb + 11 + 7) // 8 * 8
-    perm = torch.argsort(own, stable=True)
-    counts = torch.bincount(own, minlength=world)
-    packed = torch.zeros((n, rec), dtype=torch.uint8, device=rows.device)
-    packed[:, :rowb] = rows.view(torch.uint8)
-    packed[:, rowb:rowb + 8] = order.view(torch.uint8).reshape(n, 8)
-    packed[:, rowb + 8:rowb + 10] = lens
-    packed[:, rowb + 10] = status
-    send = packed[perm]
-    rc = torch.empty_like(counts)
-    dist.all_to_all_single(rc, counts, group=group)
-    rcl, scl = [int(v) for v in rc.tolist()], [int(v) for v in counts.tolist()]
-    recv = torch.empty((sum(rcl), rec), dtype=torch.uint8, device=rows.device)
-    dist.all_to_all_single(recv, send, output_split_sizes=rcl, input_split_sizes=scl, group=group)
-    r_rows = recv[:, :rowb].contiguous().view(torch.int8)
-    r_ord = recv[:, rowb:rowb + 8].contiguous().view(torch.int64).reshape(-1)
-    r_len = recv[:, rowb + 8:rowb + 10].contiguous()
-    r_st = recv[:, rowb + 10].contiguous()
-    return r_rows, r_ord, r_len, r_st, rec * (n - scl[dist.get_rank(group)])
+def record_bytes(rowb):
+    """row | int64 order | len0 | len1 | status | pad  (acx_bfs_record_bytes)"""
+    return (rowb + 7) // 8 * 8 + 16
+
+
+_POP_LUT = {}
+
+
+def popcount_lut(mask):
+    """popcount of 12-bit masks through a 4096-entry table (one gather)"""
+    key = str(mask.device)
+    if key not in _POP_LUT:
+        _POP_LUT[key] = popcount12(torch.arange(4096, dtype=torch.int64, device=mask.device))
+    return _POP_LUT[key][mask.to(torch.int64)]
 
 
 class GpuShard:
@@ -67,6 +61,7 @@ class GpuShard:
 
     def __init__(self, m, cyclical, cap_local, max_cand, device):
         self.m, self.rowb, self.cyc = m, 2 * m, bool(cyclical)
+        self.rec = record_bytes(self.rowb)
         self.dev = torch.device(device)
         self.stream = _prep(self.dev)
         d = self.dev
@@ -78,50 +73,67 @@ class GpuShard:
         self.action = torch.zeros((self.cap,), dtype=torch.uint8, device=d)
         self.total = torch.zeros((self.cap,), dtype=torch.int16, device=d)
         self.table = torch.zeros((self.tcap,), dtype=torch.int64, device=d)
-        self.n_local = 0
+        self.n_local_dev = torch.zeros((1,), dtype=torch.int64, device=d)
         self.L = _lib.lib()
+        assert self.L.acx_bfs_record_bytes(m) == self.rec
+
+    def owner_of_row(self, row, world):
+        r = torch.from_numpy(np.ascontiguousarray(row[None, :])).to(self.dev)
+        h = torch.empty((1,), dtype=torch.int64, device=self.dev)
+        _lib.check(self.L.acx_rows_hash(_ptr(r), 1, self.m, _ptr(h), self.stream), "acx_rows_hash")
+        return int(owner_of(h, world)[0])
 
     def seed(self, root):
         self.nodes[0].copy_(torch.from_numpy(root))
         self.total[0] = int(np.count_nonzero(root))
         self.gid[0] = 0
         _lib.check(self.L.acx_bfs_seed(_ptr(self.nodes), self.m, _ptr(self.table), self.tcap, 0, self.stream), "acx_bfs_seed")
-        self.n_local = 1
+        self.n_local_dev.fill_(1)
 
-    def hashes(self, rows):
-        h = torch.empty((rows.shape[0],), dtype=torch.int64, device=self.dev)
-        _lib.check(self.L.acx_rows_hash(_ptr(rows), rows.shape[0], self.m, _ptr(h), self.stream), "acx_rows_hash")
-        return h
+    def n_local(self):
+        return int(self.n_local_dev.item())
 
-    def expand(self, rows):
+    def bucket(self, rows, parent_ord, world):
+        """expand `rows` (12 children each) and group the candidate records by owner rank"""
         f = rows.shape[0]
-        ch = torch.empty((f * 12, self.rowb), dtype=torch.int8, device=self.dev)
-        ln = torch.empty((f * 12, 2), dtype=torch.uint8, device=self.dev)
-        st = torch.empty((f * 12,), dtype=torch.uint8, device=self.dev)
-        if f:
-            _lib.check(self.L.acx_expand12(_ptr(rows), _ptr(ch), _ptr(ln), _ptr(st), f, self.m, int(self.cyc), self.stream),
-                       "acx_expand12")
-        return ch, ln, st
+        n = 12 * f
+        d = self.dev
+        send = torch.empty((n, self.rec), dtype=torch.uint8, device=d)
+        counts = torch.zeros((world,), dtype=torch.int64, device=d)
+        if f == 0:
+            return send, counts
+        ch = torch.empty((n, self.rowb), dtype=torch.int8, device=d)
+        ln = torch.empty((n, 2), dtype=torch.uint8, device=d)
+        st = torch.empty((n,), dtype=torch.uint8, device=d)
+        _lib.check(self.L.acx_expand12(_ptr(rows), _ptr(ch), _ptr(ln), _ptr(st), f, self.m, int(self.cyc), self.stream), "acx_expand12")
+        own = torch.empty((n,), dtype=torch.uint8, device=d)
+        po = parent_ord.contiguous()
+        _lib.check(self.L.acx_bfs_bucket(_ptr(ch), 0, 0, 0, n, self.m, world, _ptr(own), _ptr(counts), 0, 0, 0, 0, self.stream),
+                   "acx_bfs_bucket")
+        offsets = torch.cumsum(counts, 0) - counts
+        cursor = torch.zeros((world,), dtype=torch.int64, device=d)
+        _lib.check(self.L.acx_bfs_bucket(_ptr(ch), _ptr(ln), _ptr(st), _ptr(po), n, self.m, world, _ptr(own), _ptr(counts),
+                                         _ptr(offsets), _ptr(cursor), _ptr(send), 1, self.stream), "acx_bfs_bucket")
+        return send, counts
 
-    def probe(self, cand, lens, status, order):
-        n = cand.shape[0]
+    def probe(self, recv, n_parents):
+        n = recv.shape[0]
         slot = torch.empty((n,), dtype=torch.int64, device=self.dev)
-        is_new = torch.zeros((n,), dtype=torch.uint8, device=self.dev)
+        mask = torch.zeros((n_parents,), dtype=torch.int32, device=self.dev)
         mins = torch.full((2,), -1, dtype=torch.int64, device=self.dev)
         if n:
-            _lib.check(self.L.acx_bfs_probe(_ptr(cand), _ptr(lens), _ptr(status), _ptr(order), n, self.m, _ptr(self.table),
-                                            self.tcap, _ptr(self.nodes), _ptr(slot), mins[0:].data_ptr(), mins[1:].data_ptr(),
-                                            0, _ptr(is_new), self.stream), "acx_bfs_probe")
+            _lib.check(self.L.acx_bfs_probe_packed(_ptr(recv), n, self.m, _ptr(self.table), self.tcap, _ptr(self.nodes), _ptr(slot),
+                                                   _ptr(mins), _ptr(mask), self.stream), "acx_bfs_probe_packed")
         mins = torch.where(mins < 0, torch.full_like(mins, SENT), mins)
-        return slot, is_new, mins
+        return slot, mask, mins
 
-    def commit(self, cand, lens, slot, is_new, excl, order, parent_base):
-        n = cand.shape[0]
+    def commit(self, recv, slot, excl_par, gmask, parent_base, gid_base):
+        n = recv.shape[0]
         if n:
-            _lib.check(self.L.acx_bfs_commit(_ptr(cand), _ptr(lens), _ptr(slot), _ptr(is_new), _ptr(excl), _ptr(order),
-                                             parent_base, n, n, self.m, _ptr(self.table), _ptr(self.nodes), _ptr(self.parent),
-                                             _ptr(self.action), self.total.data_ptr(), self.n_local, self.stream),
-                       "acx_bfs_commit")
+            _lib.check(self.L.acx_bfs_commit_packed(_ptr(recv), n, self.m, _ptr(slot), _ptr(excl_par), _ptr(gmask), parent_base,
+                                                    gid_base, _ptr(self.n_local_dev), _ptr(self.table), _ptr(self.nodes),
+                                                    _ptr(self.gid), _ptr(self.parent), _ptr(self.action), self.total.data_ptr(),
+                                                    self.stream), "acx_bfs_commit_packed")
 
 
 class ShardedBFS:
@@ -135,11 +147,23 @@ class ShardedBFS:
         self.dev = shard.dev
         self.n_nodes, self.n_expanded, self.levels = 1, 0, []
         self.comm_bytes = 0
+        self.timers = None  # set to {} to collect a per-phase wall-clock breakdown (adds a device sync per phase)
+        self._t0 = 0.0
+
+    def _tick(self, name):
+        if self.timers is None:
+            return
+        if self.dev.type == "cuda":
+            torch.cuda.synchronize(self.dev)
+        now = time.perf_counter()
+        if name is not None:
+            self.timers[name] = self.timers.get(name, 0.0) + now - self._t0
+        self._t0 = now
 
     def _lookup(self, gid):
         """(parent gid, action, total) of node `gid`, from whichever rank owns it"""
         s = self.shard
-        hit = torch.nonzero(s.gid[: s.n_local] == gid).flatten()
+        hit = torch.nonzero(s.gid[: s.n_local()] == gid).flatten()
         rec = torch.zeros((3,), dtype=torch.int64, device=self.dev)
         if hit.numel():
             k = hit[0]
@@ -158,72 +182,67 @@ class ShardedBFS:
 
     def run(self):
         s, G, dev = self.shard, self.world, self.dev
-        h0 = s.hashes(torch.from_numpy(self.root[None, :].copy()).to(dev))
-        if int(owner_of(h0, G)[0]) == self.rank:
+        if s.owner_of_row(self.root, G) == self.rank:
             s.seed(self.root)
         lo, hi = 0, 1
-        level_first_local = 0  # local index of the first node this rank discovered in the current frontier level
+        first = 0  # local index of the first node this rank discovered in the current frontier level
         while lo < hi:
             self.levels.append(hi - lo)
-            loc = torch.arange(level_first_local, s.n_local, device=dev)
-            gids = s.gid[level_first_local: s.n_local]
-            gids, perm = torch.sort(gids)  # local frontier in global discovery order
-            loc = loc[perm]
-            level_first_local = s.n_local
-            for off in range(lo, hi, self.chunk):
+            self._tick(None)
+            n_local = s.n_local()
+            gids, perm = torch.sort(s.gid[first:n_local])  # local frontier in global discovery order
+            loc = perm + first
+            first = n_local
+            bounds = torch.arange(lo, hi + self.chunk, self.chunk, device=dev).clamp_(max=hi)
+            cuts = torch.searchsorted(gids, bounds).tolist()
+            self._tick("level_sort")
+            for k, off in enumerate(range(lo, hi, self.chunk)):
                 C = min(self.chunk, hi - off)
-                a, b = torch.searchsorted(gids, torch.tensor([off, off + C], device=dev)).tolist()
+                a, b = cuts[k], cuts[k + 1]
                 rows = s.nodes[loc[a:b]]
-                ch, ln, st = s.expand(rows)
-                order = ((gids[a:b] - off) * 12)[:, None] + torch.arange(12, device=dev)[None, :]
-                order = order.reshape(-1)
-                own = owner_of(s.hashes(ch), G)
-                r_rows, r_ord, r_len, r_st, sent = exchange(ch, order, ln, st, own, G, self.group)
-                self.comm_bytes += sent
-                slot, is_new, mins = s.probe(r_rows, r_len, r_st, r_ord)
-                par_idx, act = r_ord // 12, r_ord % 12
-                mask = torch.zeros((C,), dtype=torch.int32, device=dev)
-                mask.scatter_add_(0, par_idx, (is_new.to(torch.int64) << act).to(torch.int32))
+                send, counts = s.bucket(rows, gids[a:b] - off, G)
+                self._tick("expand_bucket")
+                rc = torch.empty_like(counts)
+                dist.all_to_all_single(rc, counts, group=self.group)
+                rcl, scl = [int(v) for v in rc.tolist()], [int(v) for v in counts.tolist()]
+                recv = torch.empty((sum(rcl), send.shape[1]), dtype=torch.uint8, device=dev)
+                dist.all_to_all_single(recv, send, output_split_sizes=rcl, input_split_sizes=scl, group=self.group)
+                self.comm_bytes += send.shape[1] * (send.shape[0] - scl[self.rank])
+                self._tick("all_to_all")
+                slot, mask, mins = s.probe(recv, C)
+                self._tick("probe")
                 dist.all_reduce(mask, group=self.group)
                 dist.all_reduce(mins, op=dist.ReduceOp.MIN, group=self.group)
-                mask = mask.to(torch.int64)
-                cnt = popcount12(mask)
+                cnt = popcount_lut(mask)
                 cum = torch.cumsum(cnt, dim=0)
-                seen_after = cum + self.n_nodes
-                over = seen_after >= self.budget
-                pstar = torch.argmax(over.to(torch.uint8))
-                head = torch.stack([mins[0], mins[1], over.any().to(torch.int64), pstar, seen_after[pstar], cum[-1]]).tolist()
-                c_s, c_e = int(head[0]), int(head[1])
-                p_star = int(head[3]) if head[2] else None
+                c_s, c_e, n_new = torch.cat([mins, cum[-1:]]).tolist()
+                self._tick("reduce_scan")
                 events = []
                 if c_s < SENT:
                     events.append((c_s, 0, "solved"))
                 if c_e < SENT:
                     events.append((c_e, 0, "error"))
-                if p_star is not None:
+                p_star = None
+                if self.n_nodes + n_new >= self.budget:
+                    # first parent after which len(tree_nodes) >= max_nodes_to_explore (breadth_first.py:91-95)
+                    p_star = int(torch.searchsorted(cum, torch.tensor([self.budget - self.n_nodes], device=dev))[0])
                     events.append((12 * p_star + 11, 1, "budget"))
                 if events:
                     pos, _, what = min(events)
                     if what == "solved":
                         self.n_expanded += pos // 12 + 1
                         p, aa = pos // 12, pos % 12
-                        before = int(cum[p] - cnt[p]) + int(popcount12(mask[p] & ((1 << aa) - 1)))
+                        before = int(cum[p] - cnt[p]) + int(popcount12(mask[p].to(torch.int64) & ((1 << aa) - 1)))
                         self.n_nodes += before
                         return True, self._path(off + p, aa)
                     if what == "error":
                         raise AssertionError("a relator became empty during the search: not a valid presentation")
                     self.n_expanded += p_star + 1
-                    self.n_nodes = int(head[4])
+                    self.n_nodes += int(cum[p_star])
                     return False, None
-                excl_par = cum - cnt
-                grank = excl_par[par_idx] + popcount12(mask[par_idx] & ((1 << act) - 1))
-                lex = torch.cumsum(is_new.to(torch.int64), dim=0) - is_new
-                s.commit(r_rows, r_len, slot, is_new, lex, r_ord, off)
-                sel = is_new.bool()
-                n_new_local = int(sel.sum())
-                s.gid[s.n_local + lex[sel]] = self.n_nodes + grank[sel]
-                s.n_local += n_new_local
-                self.n_nodes += int(head[5])
+                s.commit(recv, slot, cum - cnt, mask, off, self.n_nodes)
+                self._tick("commit")
+                self.n_nodes += n_new
                 self.n_expanded += C
             lo, hi = hi, self.n_nodes
         return False, None

@@ -194,6 +194,191 @@ __global__ void k_bfs_seed(const int8_t* row, int rowb, uint64_t* table, int64_t
     table[slot] = tag | (uint64_t)id;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Sharded bfs: candidate records travel between GPUs as  row | order (8) | lens (2) | status (1) | pad,
+// rec = align8(rowb) + 16 bytes.  owner(state) = ((hash >> 20) & 0x7fffffff) % world.
+__device__ __forceinline__ int bfs_owner(uint64_t h, int world) { return (int)(((h >> 20) & 0x7FFFFFFFull) % (uint64_t)world); }
+
+// pass 1: owner of every candidate + per-owner counts (block histogram, one global atomic per owner per block)
+__global__ void k_bfs_bucket_count(const int8_t* cand, int64_t n, int rowb, int world, uint8_t* owner, unsigned long long* counts) {
+    __shared__ unsigned int s_cnt[64];
+    if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0u;
+    __syncthreads();
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) {
+        const int o = bfs_owner(bfs_row_hash(reinterpret_cast<const uint32_t*>(cand + j * rowb), rowb / 4), world);
+        owner[j] = (uint8_t)o;
+        atomicAdd(&s_cnt[o], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < world && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+}
+
+// pass 2: scatter the records into the send buffer, grouped by owner (order inside a group is free:
+// order numbers travel with the rows and the receiver resolves first discovery by them)
+__global__ void k_bfs_bucket_scatter(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* parent_ord,
+                                     const uint8_t* owner, int64_t n, int rowb, int rec, int world, const int64_t* offsets,
+                                     unsigned long long* cursor, uint8_t* send) {
+    __shared__ unsigned int s_cnt[64];
+    __shared__ unsigned long long s_base[64];
+    if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0u;
+    __syncthreads();
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int o = 0;
+    unsigned int r = 0;
+    if (j < n) {
+        o = owner[j];
+        r = atomicAdd(&s_cnt[o], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < world && s_cnt[threadIdx.x])
+        s_base[threadIdx.x] = atomicAdd(&cursor[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+    __syncthreads();
+    if (j >= n) return;
+    uint8_t* dst = send + ((int64_t)offsets[o] + (int64_t)s_base[o] + r) * rec;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(cand + j * rowb);
+    uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+    for (int k = 0; k < rowb / 4; ++k) d4[k] = src[k];
+    const int off = (rowb + 7) / 8 * 8;
+    if (off != rowb) d4[rowb / 4] = 0u;
+    *reinterpret_cast<int64_t*>(dst + off) = parent_ord[j / 12] * 12 + (j % 12);
+    *reinterpret_cast<uint32_t*>(dst + off + 8) = (uint32_t)lens[2 * j] | ((uint32_t)lens[2 * j + 1] << 8) | ((uint32_t)status[j] << 16);
+    *reinterpret_cast<uint32_t*>(dst + off + 12) = 0u;
+}
+
+struct PackedParams {
+    const uint8_t* recs;  // [n, rec]
+    int64_t n;
+    int rowb, rec;
+    uint64_t* table;
+    int64_t tcap;
+    const int8_t* nodes;
+    int64_t* slot;        // [n] scratch
+    unsigned long long* mins;  // [2] min success order, min error order
+    int* mask;            // [C] per-parent 12-bit "new" mask of this round (atomicOr)
+    // commit
+    const int64_t* excl_par;  // [C] exclusive scan of the global per-parent new counts
+    const int* gmask;         // [C] global masks (after the all-reduce)
+    int64_t parent_base, gid_base;
+    unsigned long long* n_local;  // device counter of local nodes
+    int8_t* nodes_w;
+    int64_t* gid;
+    int64_t* parent;
+    uint8_t* action;
+    uint16_t* total;
+};
+
+__device__ __forceinline__ int64_t rec_order(const PackedParams& p, int64_t j) {
+    return *reinterpret_cast<const int64_t*>(p.recs + j * p.rec + (p.rowb + 7) / 8 * 8);
+}
+
+__global__ void k_bfs_probe_packed(const PackedParams p) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= p.n) return;
+    const int nwords = p.rowb / 4, off = (p.rowb + 7) / 8 * 8;
+    const uint8_t* rec = p.recs + j * p.rec;
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(rec);
+    const int64_t ord = *reinterpret_cast<const int64_t*>(rec + off);
+    const uint32_t meta = *reinterpret_cast<const uint32_t*>(rec + off + 8);
+    if ((meta >> 16) & 0xFFu) {
+        atomicMin(p.mins + 1, (unsigned long long)ord);
+        p.slot[j] = -2;
+        return;
+    }
+    if ((int)(meta & 0xFFu) + (int)((meta >> 8) & 0xFFu) == 2) {
+        atomicMin(p.mins, (unsigned long long)ord);
+        p.slot[j] = -2;
+        return;
+    }
+    const uint64_t h = bfs_row_hash(row, nwords);
+    const uint64_t tag = ((h >> 48) | 1ull) << 48;
+    const uint64_t mine = tag | PROV_BIT | (uint64_t)j;
+    const uint64_t mask = (uint64_t)p.tcap - 1;
+    uint64_t slot = (h ^ (h >> 23)) & mask;
+    for (;;) {
+        uint64_t e = __ldcg(p.table + slot);
+        if (e == 0ull) {
+            const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(p.table + slot), 0ull, (unsigned long long)mine);
+            if (old == 0ull) {
+                p.slot[j] = (int64_t)slot;
+                return;
+            }
+            e = old;
+        }
+        if ((e >> 48) == (tag >> 48)) {
+            if (e & PROV_BIT) {
+                for (;;) {
+                    const int64_t other = (int64_t)(e & VAL_MASK);
+                    if (other == j) {
+                        p.slot[j] = (int64_t)slot;
+                        return;
+                    }
+                    if (!bfs_rows_equal(row, reinterpret_cast<const uint32_t*>(p.recs + other * p.rec), nwords)) break;
+                    if (rec_order(p, other) < ord) {
+                        p.slot[j] = (int64_t)slot;
+                        return;
+                    }
+                    const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(p.table + slot), (unsigned long long)e,
+                                                   (unsigned long long)mine);
+                    if (old == e) {
+                        p.slot[j] = (int64_t)slot;
+                        return;
+                    }
+                    e = old;
+                    if (!(e & PROV_BIT)) break;
+                }
+            } else {
+                const int64_t id = (int64_t)(e & VAL_MASK);
+                if (bfs_rows_equal(row, reinterpret_cast<const uint32_t*>(p.nodes + id * p.rowb), nwords)) {
+                    p.slot[j] = -1;
+                    return;
+                }
+            }
+        }
+        slot = (slot + 1) & mask;
+    }
+}
+
+// new candidates set their bit in the per-parent mask of the round
+__global__ void k_bfs_resolve_packed(const PackedParams p) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= p.n) return;
+    const int64_t s = p.slot[j];
+    if (s < 0) return;
+    const uint64_t e = p.table[s];
+    if ((e & PROV_BIT) && (int64_t)(e & VAL_MASK) == j) {
+        const int64_t ord = rec_order(p, j);
+        atomicOr(p.mask + ord / 12, 1 << (int)(ord % 12));
+    } else {
+        p.slot[j] = -1;  // a duplicate inside the round
+    }
+}
+
+// new candidates become local nodes; their global id follows from the all-reduced masks
+__global__ void k_bfs_commit_packed(const PackedParams p) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= p.n) return;
+    const int64_t s = p.slot[j];
+    if (s < 0) return;
+    const int off = (p.rowb + 7) / 8 * 8;
+    const uint8_t* rec = p.recs + j * p.rec;
+    const int64_t ord = *reinterpret_cast<const int64_t*>(rec + off);
+    const uint32_t meta = *reinterpret_cast<const uint32_t*>(rec + off + 8);
+    const int64_t par = ord / 12;
+    const int act = (int)(ord % 12);
+    const int64_t gid = p.gid_base + p.excl_par[par] + __popc((unsigned)p.gmask[par] & ((1u << act) - 1u));
+    const int64_t id = (int64_t)atomicAdd(p.n_local, 1ull);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(rec);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(p.nodes_w + id * p.rowb);
+    for (int k = 0; k < p.rowb / 4; ++k) dst[k] = src[k];
+    p.gid[id] = gid;
+    p.parent[id] = p.parent_base + par;
+    p.action[id] = (uint8_t)act;
+    p.total[id] = (uint16_t)((meta & 0xFFu) + ((meta >> 8) & 0xFFu));
+    const uint64_t e = p.table[s];
+    p.table[s] = (e & ~(PROV_BIT | VAL_MASK)) | (uint64_t)id;
+}
+
 }  // namespace acx
 
 using namespace acx;
@@ -245,6 +430,59 @@ extern "C" int acx_rows_hash(const int8_t* rows, int64_t n, int m, uint64_t* has
     if (n == 0) return ACX_OK;
     if (!rows || !hash_out) return acx_fail(ACX_ERR_ARG, "acx_rows_hash: null pointer");
     k_rows_hash<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rows, n, 2 * m, hash_out);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+extern "C" int acx_bfs_record_bytes(int m) { return (2 * m + 7) / 8 * 8 + 16; }
+
+extern "C" int acx_bfs_bucket(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* parent_ord,
+                              int64_t n, int m, int world, uint8_t* owner_scratch, uint64_t* counts, int64_t* offsets,
+                              uint64_t* cursor, uint8_t* send, int phase, acx_stream_t stream) {
+    if (n < 0 || m < 1 || (2 * m) % 4 != 0 || world < 1 || world > 64) return acx_fail(ACX_ERR_ARG, "acx_bfs_bucket: bad argument (m even, 1 <= world <= 64)");
+    if (n == 0) return ACX_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (phase == 0) {
+        if (!cand || !owner_scratch || !counts) return acx_fail(ACX_ERR_ARG, "acx_bfs_bucket: null pointer");
+        k_bfs_bucket_count<<<grid, 256, 0, st>>>(cand, n, 2 * m, world, owner_scratch, reinterpret_cast<unsigned long long*>(counts));
+    } else {
+        if (!cand || !lens || !status || !parent_ord || !owner_scratch || !offsets || !cursor || !send) return acx_fail(ACX_ERR_ARG, "acx_bfs_bucket: null pointer");
+        k_bfs_bucket_scatter<<<grid, 256, 0, st>>>(cand, lens, status, parent_ord, owner_scratch, n, 2 * m, acx_bfs_record_bytes(m), world,
+                                                   offsets, reinterpret_cast<unsigned long long*>(cursor), send);
+    }
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+extern "C" int acx_bfs_probe_packed(const uint8_t* recs, int64_t n, int m, uint64_t* table, int64_t tcap, const int8_t* nodes,
+                                    int64_t* slot, uint64_t* mins, int32_t* mask, acx_stream_t stream) {
+    if (n < 0 || m < 1 || (2 * m) % 4 != 0 || tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe_packed: bad argument");
+    if (n == 0) return ACX_OK;
+    if (!recs || !table || !nodes || !slot || !mins || !mask) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe_packed: null pointer");
+    PackedParams p = {};
+    p.recs = recs; p.n = n; p.rowb = 2 * m; p.rec = acx_bfs_record_bytes(m); p.table = table; p.tcap = tcap; p.nodes = nodes;
+    p.slot = slot; p.mins = reinterpret_cast<unsigned long long*>(mins); p.mask = mask;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    k_bfs_probe_packed<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    k_bfs_resolve_packed<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+extern "C" int acx_bfs_commit_packed(const uint8_t* recs, int64_t n, int m, const int64_t* slot, const int64_t* excl_par,
+                                     const int32_t* gmask, int64_t parent_base, int64_t gid_base, uint64_t* n_local,
+                                     uint64_t* table, int8_t* nodes, int64_t* gid, int64_t* parent, uint8_t* action,
+                                     uint16_t* total, acx_stream_t stream) {
+    if (n < 0 || m < 1 || (2 * m) % 4 != 0) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit_packed: bad argument");
+    if (n == 0) return ACX_OK;
+    if (!recs || !slot || !excl_par || !gmask || !n_local || !table || !nodes || !gid || !parent || !action || !total) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit_packed: null pointer");
+    PackedParams p = {};
+    p.recs = recs; p.n = n; p.rowb = 2 * m; p.rec = acx_bfs_record_bytes(m); p.table = table; p.slot = const_cast<int64_t*>(slot);
+    p.excl_par = excl_par; p.gmask = gmask; p.parent_base = parent_base; p.gid_base = gid_base;
+    p.n_local = reinterpret_cast<unsigned long long*>(n_local); p.nodes_w = nodes; p.gid = gid; p.parent = parent; p.action = action;
+    p.total = total;
+    k_bfs_commit_packed<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }

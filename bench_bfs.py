@@ -34,8 +34,9 @@ def run(dev, budget=10 ** 7, chunk=1 << 20):
             "reference": "660 expanded nodes/s, 5.6k discovered nodes/s at budget 1e5 (SURVEY.md section 6)"}
 
 
-def run_sharded(budget=10 ** 8, chunk=1 << 20):
-    """torchrun entry: hash-partitioned bfs over WORLD_SIZE GPUs, strong scaling at a fixed budget."""
+def run_sharded(budget=10 ** 8, chunk_per_rank=1 << 20):
+    """torchrun entry: hash-partitioned bfs over WORLD_SIZE GPUs, strong scaling at a fixed budget.
+    A round expands `chunk_per_rank` parents per rank (the result does not depend on the chunk)."""
     import torch.distributed as dist
 
     from acx.bfs_sharded import GpuShard, ShardedBFS
@@ -46,11 +47,14 @@ def run_sharded(budget=10 ** 8, chunk=1 << 20):
     os.environ["NCCL_DEBUG"] = "WARN"
     dist.init_process_group("nccl", device_id=dev)
     out = None
-    for b in (10 ** 5, budget):  # first pass = warm-up (NCCL channels, kernels)
-        cap_local = int(b / world * 1.25) + 4096
-        max_cand = int(12 * chunk / world * 1.25) + 4096
+    chunk = chunk_per_rank * world
+    for b in (10 ** 6, budget):  # first pass = warm-up (NCCL channels, kernels)
+        cap_local = int(b / world * (1.0 if world == 1 else 1.06)) + 4096
+        max_cand = int(12 * chunk / world * 1.1) + 4096
         shard = GpuShard(36, False, cap_local, max_cand, str(dev))
         eng = ShardedBFS(ak3(), b, shard, chunk=chunk)
+        if os.environ.get("ACX_BFS_PROF"):
+            eng.timers = {}
         dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -63,7 +67,9 @@ def run_sharded(budget=10 ** 8, chunk=1 << 20):
         out = {"config": "configs[3] hash-partitioned level-synchronous bfs from AK(3), m=36, budget %d" % b,
                "n_gpus": world, "solved": ok, "n_seen": eng.n_nodes, "nodes_expanded": eng.n_expanded, "wall_s": float(dt[0]),
                "nodes_expanded_per_s": eng.n_expanded / float(dt[0]), "all_to_all_bytes_total": int(sent[0]),
-               "scaling": "strong", "levels": eng.levels}
+               "scaling": "strong", "chunk_parents_per_round": chunk, "levels": eng.levels}
+        if eng.timers is not None:
+            out["phase_s_rank0"] = {k: round(v, 5) for k, v in eng.timers.items()}
     if rank == 0:
         import json
         print(json.dumps(out))
@@ -71,7 +77,8 @@ def run_sharded(budget=10 ** 8, chunk=1 << 20):
 
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "sharded":
-    run_sharded(int(float(sys.argv[2])) if len(sys.argv) > 2 else 10 ** 8)
+    run_sharded(int(float(sys.argv[2])) if len(sys.argv) > 2 else 10 ** 8,
+                int(float(sys.argv[3])) if len(sys.argv) > 3 else 1 << 20)
 elif __name__ == "__main__":
     import json
 

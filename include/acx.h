@@ -142,6 +142,26 @@ int acx_bfs_commit(const int8_t* cand, const uint8_t* lens, const int64_t* slot,
                    int64_t node_base, acx_stream_t stream);
 int acx_rows_hash(const int8_t* rows, int64_t n, int m, uint64_t* hash_out, acx_stream_t stream);
 
+/* Hash-partitioned (multi-GPU) bfs: candidates travel to their owner rank as packed records
+ *     row (2m bytes, padded to 8) | int64 order | uint8 len0 | uint8 len1 | uint8 status | pad   (acx_bfs_record_bytes)
+ * with owner(state) = ((hash >> 20) & 0x7fffffff) % world.
+ *   acx_bfs_bucket        phase 0: owner of each candidate + per-owner counts; phase 1: scatter the records into
+ *                         `send`, grouped by owner at offsets[] (exclusive scan of counts), ready for the all-to-all-v.
+ *                         order of candidate j = parent_ord[j / 12] * 12 + j % 12.
+ *   acx_bfs_probe_packed  acx_bfs_probe on received records; new candidates OR their bit into mask[order / 12].
+ *   acx_bfs_commit_packed new candidates become local nodes; global id = gid_base + excl_par[p] +
+ *                         popcount(gmask[p] & bits below the action), from the all-reduced masks. */
+int acx_bfs_record_bytes(int m);
+int acx_bfs_bucket(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* parent_ord, int64_t n,
+                   int m, int world, uint8_t* owner_scratch, uint64_t* counts, int64_t* offsets, uint64_t* cursor,
+                   uint8_t* send, int phase, acx_stream_t stream);
+int acx_bfs_probe_packed(const uint8_t* recs, int64_t n, int m, uint64_t* table, int64_t tcap, const int8_t* nodes,
+                         int64_t* slot, uint64_t* mins, int32_t* mask, acx_stream_t stream);
+int acx_bfs_commit_packed(const uint8_t* recs, int64_t n, int m, const int64_t* slot, const int64_t* excl_par,
+                          const int32_t* gmask, int64_t parent_base, int64_t gid_base, uint64_t* n_local, uint64_t* table,
+                          int8_t* nodes, int64_t* gid, int64_t* parent, uint8_t* action, uint16_t* total,
+                          acx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

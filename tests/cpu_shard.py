@@ -18,7 +18,8 @@ class OracleShard:
         self.parent = torch.full((cap_local,), -1, dtype=torch.int64)
         self.action = torch.zeros((cap_local,), dtype=torch.uint8)
         self.total = torch.zeros((cap_local,), dtype=torch.int16)
-        self.n_local = 0
+        self._n = 0
+        self.rec = (self.rowb + 7) // 8 * 8 + 16
         self.table = {}  # row bytes -> ("node", idx) | ("cand", j)
 
     def seed(self, root):
@@ -26,61 +27,87 @@ class OracleShard:
         self.total[0] = int(np.count_nonzero(root))
         self.gid[0] = 0
         self.table[root.tobytes()] = ("node", 0)
-        self.n_local = 1
+        self._n = 1
 
-    def hashes(self, rows):
-        a = rows.numpy().view(np.uint8).astype(np.uint64)
+    def n_local(self):
+        return self._n
+
+    def _hash(self, a):
+        a = a.view(np.uint8).astype(np.uint64)
         h = np.full(a.shape[0], 1469598103934665603, dtype=np.uint64)
         with np.errstate(over="ignore"):
             for k in range(a.shape[1]):
                 h = (h ^ a[:, k]) * np.uint64(1099511628211)
             h ^= h >> np.uint64(29)
-        return torch.from_numpy(h.view(np.int64).copy())
+        return h
 
-    def expand(self, rows):
+    def owner_of_row(self, row, world):
+        return int(((self._hash(np.ascontiguousarray(row[None, :])) >> np.uint64(20)) & np.uint64(0x7FFFFFFF))[0] % world)
+
+    def bucket(self, rows, parent_ord, world):
         f = rows.shape[0]
-        if f == 0:
-            return (torch.empty((0, self.rowb), dtype=torch.int8), torch.empty((0, 2), dtype=torch.uint8),
-                    torch.empty((0,), dtype=torch.uint8))
-        ch, ln, st = ac_oracle.expand12_batch(rows.numpy(), cyclical=self.cyc)
-        return (torch.from_numpy(ch.reshape(f * 12, self.rowb)), torch.from_numpy(ln.reshape(f * 12, 2).astype(np.uint8)),
-                torch.from_numpy(st.reshape(f * 12)))
+        n = 12 * f
+        off = (self.rowb + 7) // 8 * 8
+        send = np.zeros((n, self.rec), dtype=np.uint8)
+        counts = np.zeros(world, dtype=np.int64)
+        if f:
+            ch, ln, st = ac_oracle.expand12_batch(rows.numpy(), cyclical=self.cyc)
+            ch = np.ascontiguousarray(ch.reshape(n, self.rowb))
+            own = ((self._hash(ch) >> np.uint64(20)) & np.uint64(0x7FFFFFFF)) % np.uint64(world)
+            order = (parent_ord.numpy()[:, None] * 12 + np.arange(12)[None, :]).reshape(-1).astype(np.int64)
+            rec = np.zeros((n, self.rec), dtype=np.uint8)
+            rec[:, :self.rowb] = ch.view(np.uint8)
+            rec[:, off:off + 8] = order.view(np.uint8).reshape(n, 8)
+            rec[:, off + 8:off + 10] = ln.reshape(n, 2).astype(np.uint8)
+            rec[:, off + 10] = st.reshape(n)
+            # any order inside an owner group is legal: scramble it to prove the receiver does not depend on it
+            perm = np.lexsort((np.random.default_rng(n).permutation(n), own))
+            send = rec[perm]
+            counts = np.bincount(own.astype(np.int64), minlength=world).astype(np.int64)
+        return torch.from_numpy(send), torch.from_numpy(counts)
 
-    def probe(self, cand, lens, status, order):
-        n = cand.shape[0]
+    def _fields(self, recv):
+        r = recv.numpy()
+        off = (self.rowb + 7) // 8 * 8
+        rows = np.ascontiguousarray(r[:, :self.rowb]).view(np.int8)
+        order = np.ascontiguousarray(r[:, off:off + 8]).view(np.int64).reshape(-1)
+        return rows, order, r[:, off + 8:off + 10], r[:, off + 10]
+
+    def probe(self, recv, n_parents):
+        n = recv.shape[0]
+        c, o, l, s = self._fields(recv)
         slot = torch.full((n,), -1, dtype=torch.int64)
         mins = [SENT, SENT]
-        c, l, s, o = cand.numpy(), lens.numpy(), status.numpy(), order.numpy()
         keys = [None] * n
         for j in range(n):
             if s[j] != 0:
                 mins[1] = min(mins[1], int(o[j]))
-                slot[j] = -2
             elif int(l[j, 0]) + int(l[j, 1]) == 2:
                 mins[0] = min(mins[0], int(o[j]))
-                slot[j] = -2
             else:
                 key = c[j].tobytes()
                 keys[j] = key
                 e = self.table.get(key)
                 if e is None or (e[0] == "cand" and o[e[1]] > o[j]):
                     self.table[key] = ("cand", j)
-                    slot[j] = 0
-                elif e[0] == "cand":
-                    slot[j] = 0
-        is_new = torch.zeros((n,), dtype=torch.uint8)
+        mask = torch.zeros((n_parents,), dtype=torch.int32)
         for j in range(n):
             if keys[j] is not None and self.table[keys[j]] == ("cand", j):
-                is_new[j] = 1
+                slot[j] = 0
+                mask[int(o[j]) // 12] |= 1 << (int(o[j]) % 12)
         self._keys = keys
-        return slot, is_new, torch.tensor(mins, dtype=torch.int64)
+        return slot, mask, torch.tensor(mins, dtype=torch.int64)
 
-    def commit(self, cand, lens, slot, is_new, excl, order, parent_base):
-        for j in range(cand.shape[0]):
-            if is_new[j]:
-                k = self.n_local + int(excl[j])
-                self.nodes[k] = cand[j]
-                self.parent[k] = parent_base + int(order[j]) // 12
-                self.action[k] = int(order[j]) % 12
-                self.total[k] = int(lens[j, 0]) + int(lens[j, 1])
+    def commit(self, recv, slot, excl_par, gmask, parent_base, gid_base):
+        c, o, l, s = self._fields(recv)
+        for j in range(recv.shape[0]):
+            if slot[j] >= 0:
+                k = self._n
+                self._n += 1
+                par, act = int(o[j]) // 12, int(o[j]) % 12
+                self.nodes[k] = torch.from_numpy(c[j].copy())
+                self.gid[k] = gid_base + int(excl_par[par]) + bin(int(gmask[par]) & ((1 << act) - 1)).count("1")
+                self.parent[k] = parent_base + par
+                self.action[k] = act
+                self.total[k] = int(l[j, 0]) + int(l[j, 1])
                 self.table[self._keys[j]] = ("node", k)
