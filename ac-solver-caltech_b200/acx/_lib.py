@@ -28,10 +28,16 @@ _SIGNATURES = {
                               _I64, _PTR]),
     "acx_rows_hash": (_I32, [_PTR, _I64, _I32, _PTR, _PTR]),
     "acx_bfs_record_bytes": (_I32, [_I32]),
+    "acx_bfs_expand_bucket": (_I32, [_PTR, _PTR, _PTR, _I64, _I64, _I32, _I32, _I32, _I64, _PTR, _PTR, _PTR]),
     "acx_bfs_bucket": (_I32, [_PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR, _PTR, _PTR, _PTR, _PTR, _I32, _PTR]),
-    "acx_bfs_probe_packed": (_I32, [_PTR, _I64, _I32, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR]),
-    "acx_bfs_commit_packed": (_I32, [_PTR, _I64, _I32, _PTR, _PTR, _PTR, _I64, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR,
-                                     _PTR, _PTR]),
+    "acx_bfs_probe_packed": (_I32, [_PTR, _PTR, _I32, _I64, _I32, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR]),
+    "acx_bfs_commit_packed": (_I32, [_PTR, _PTR, _I32, _I64, _I32, _PTR, _PTR, _PTR, _I64, _I64, _PTR, _PTR, _PTR, _PTR, _PTR,
+                                     _PTR, _PTR, _PTR]),
+    "acx_peer_alloc": (_I32, [_I64, _PTR]),
+    "acx_peer_free": (_I32, [_PTR]),
+    "acx_peer_export": (_I32, [_PTR, _PTR]),
+    "acx_peer_open": (_I32, [_PTR, _PTR]),
+    "acx_peer_close": (_I32, [_PTR]),
     "acx_env_step": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _F32, _F32, _I32, _PTR]),
     "acx_rows_certify": (_I32, [_PTR, _I64, _I32, _PTR, _PTR, _PTR]),
 }

@@ -42,7 +42,7 @@ def owner_of(h, world):
 
 def record_bytes(rowb):
     """row | int64 order | len0 | len1 | status | pad  (acx_bfs_record_bytes)"""
-    return (rowb + 7) // 8 * 8 + 16
+    return ((rowb + 7) // 8 * 8 + 16 + 15) // 16 * 16
 
 
 _POP_LUT = {}
@@ -56,17 +56,31 @@ def popcount_lut(mask):
     return _POP_LUT[key][mask.to(torch.int64)]
 
 
-class GpuShard:
-    """One rank's shard on its GPU: rows, records and table of the states it owns (libacx kernels)."""
+class _RawCuda:
+    """device memory owned by libacx (acx_peer_alloc) exposed to torch through the CUDA array interface"""
 
-    def __init__(self, m, cyclical, cap_local, max_cand, device):
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+class GpuShard:
+    """One rank's shard on its GPU: rows, records and table of the states it owns (libacx kernels).
+
+    transport "p2p" (default for max_relator_length 36 on more than one GPU): every rank owns two peer-visible
+    receive buffers (CUDA IPC); the fused expand kernel of rank s stores each record straight into region s of
+    its owner's buffer over NVLink -- the kernel IS the all-to-all, there is no staging copy and no collective on
+    the data path (only the count all-gather, which doubles as the barrier).  transport "nccl": records are
+    bucketed into a local send buffer and exchanged with an all-to-all-v."""
+
+    def __init__(self, m, cyclical, cap_local, max_parents, device, transport="auto"):
         self.m, self.rowb, self.cyc = m, 2 * m, bool(cyclical)
         self.rec = record_bytes(self.rowb)
         self.dev = torch.device(device)
         self.stream = _prep(self.dev)
         d = self.dev
         self.cap = int(cap_local)
-        self.tcap = _next_pow2(2 * (self.cap + max_cand))
+        self.fmax = int(max_parents)
+        self.tcap = _next_pow2(2 * (self.cap + 12 * self.fmax))
         self.nodes = torch.zeros((self.cap, self.rowb), dtype=torch.int8, device=d)
         self.gid = torch.full((self.cap,), -1, dtype=torch.int64, device=d)
         self.parent = torch.full((self.cap,), -1, dtype=torch.int64, device=d)
@@ -76,6 +90,69 @@ class GpuShard:
         self.n_local_dev = torch.zeros((1,), dtype=torch.int64, device=d)
         self.L = _lib.lib()
         assert self.L.acx_bfs_record_bytes(m) == self.rec
+        self.transport = transport
+        self._own, self._opened = [], []
+        self.world = None
+
+    # -- wiring -----------------------------------------------------------------------------------------------
+    def connect(self, group=None):
+        """allocate the exchange buffers for this process group (collective: every rank calls it)"""
+        if self.world is not None:
+            return
+        G, rank = dist.get_world_size(group), dist.get_rank(group)
+        self.world, self.rank = G, rank
+        self.fused = self.m == 36 and G <= 32
+        f = self.fmax
+        self.rcap = 12 * f if G == 1 else min(12 * f, int(12 * f / G * 1.15) + 8192)
+        if self.transport == "auto":
+            self.transport = "p2p" if (self.fused and G > 1) else "nccl"
+        if self.transport == "p2p" and not (self.fused and G > 1):
+            raise ValueError("transport 'p2p' needs max_relator_length 36 and 2..32 ranks")
+        nbytes = G * self.rcap * self.rec
+        if self.transport == "p2p":
+            import ctypes
+
+            self.recv_bufs, self.dst = [], []
+            for _ in range(2):
+                ptr = ctypes.c_void_p()
+                _lib.check(self.L.acx_peer_alloc(nbytes, ctypes.byref(ptr)), "acx_peer_alloc")
+                self._own.append(ptr.value)
+                h = (ctypes.c_uint8 * 64)()
+                _lib.check(self.L.acx_peer_export(ptr, h), "acx_peer_export")
+                mine = torch.tensor(list(h), dtype=torch.uint8, device=self.dev)
+                allh = torch.empty((G * 64,), dtype=torch.uint8, device=self.dev)
+                dist.all_gather_into_tensor(allh, mine, group=group)
+                allh = allh.view(G, 64).cpu().numpy()
+                bases = []
+                for g in range(G):
+                    if g == rank:
+                        bases.append(ptr.value)
+                        continue
+                    hg = (ctypes.c_uint8 * 64)(*[int(v) for v in allh[g]])
+                    pg = ctypes.c_void_p()
+                    _lib.check(self.L.acx_peer_open(hg, ctypes.byref(pg)), "acx_peer_open")
+                    self._opened.append(pg.value)
+                    bases.append(pg.value)
+                self.recv_bufs.append(torch.as_tensor(_RawCuda(ptr.value, nbytes), device=self.dev).view(G * self.rcap, self.rec))
+                # my region inside every owner's receive buffer
+                self.dst.append([bases[g] + rank * self.rcap * self.rec for g in range(G)])
+        elif self.fused:
+            self.send = torch.empty((G * self.rcap, self.rec), dtype=torch.uint8, device=self.dev)
+            self.dst = [[self.send.data_ptr() + g * self.rcap * self.rec for g in range(G)]] * 2
+        self._group = group
+
+    def close(self):
+        """collective: nobody may still be writing into a peer buffer when it is unmapped / freed"""
+        if self._own or self._opened:
+            torch.cuda.synchronize(self.dev)
+            dist.barrier(group=self._group)
+            for p in self._opened:
+                self.L.acx_peer_close(p)
+            self.recv_bufs = []
+            dist.barrier(group=self._group)
+            for p in self._own:
+                self.L.acx_peer_free(p)
+            self._own, self._opened = [], []
 
     def owner_of_row(self, row, world):
         r = torch.from_numpy(np.ascontiguousarray(row[None, :])).to(self.dev)
@@ -93,47 +170,89 @@ class GpuShard:
     def n_local(self):
         return int(self.n_local_dev.item())
 
-    def bucket(self, rows, parent_ord, world):
-        """expand `rows` (12 children each) and group the candidate records by owner rank"""
-        f = rows.shape[0]
+    # -- one round --------------------------------------------------------------------------------------------
+    def stage(self, loc, gids, ord_base, k):
+        """expand the parents nodes[loc] (global ids `gids`) and route the candidate records towards their owners.
+        Returns counts int64[world + 1] on the device: records for each owner, then a region-overflow flag."""
+        import ctypes
+
+        G, f, d = self.world, loc.shape[0], self.dev
+        if f > self.fmax:
+            raise RuntimeError("sharded bfs: %d local parents in one round, buffers sized for %d" % (f, self.fmax))
         n = 12 * f
-        d = self.dev
-        send = torch.empty((n, self.rec), dtype=torch.uint8, device=d)
-        counts = torch.zeros((world,), dtype=torch.int64, device=d)
+        counts = torch.zeros((G + 1,), dtype=torch.int64, device=d)
+        self._packed = None
         if f == 0:
-            return send, counts
+            return counts
+        loc, gids = loc.contiguous(), gids.contiguous()
+        if self.fused:
+            dst = (ctypes.c_void_p * G)(*self.dst[k % 2])
+            _lib.check(self.L.acx_bfs_expand_bucket(_ptr(self.nodes), _ptr(loc), _ptr(gids), int(ord_base), f, self.m,
+                                                    int(self.cyc), G, self.rcap, _ptr(counts), dst, self.stream),
+                       "acx_bfs_expand_bucket")
+            return counts
+        rows = self.nodes[loc]
+        send = torch.empty((n, self.rec), dtype=torch.uint8, device=d)
         ch = torch.empty((n, self.rowb), dtype=torch.int8, device=d)
         ln = torch.empty((n, 2), dtype=torch.uint8, device=d)
         st = torch.empty((n,), dtype=torch.uint8, device=d)
         _lib.check(self.L.acx_expand12(_ptr(rows), _ptr(ch), _ptr(ln), _ptr(st), f, self.m, int(self.cyc), self.stream), "acx_expand12")
         own = torch.empty((n,), dtype=torch.uint8, device=d)
-        po = parent_ord.contiguous()
-        _lib.check(self.L.acx_bfs_bucket(_ptr(ch), 0, 0, 0, n, self.m, world, _ptr(own), _ptr(counts), 0, 0, 0, 0, self.stream),
+        po = (gids - ord_base).contiguous()
+        _lib.check(self.L.acx_bfs_bucket(_ptr(ch), 0, 0, 0, n, self.m, G, _ptr(own), _ptr(counts), 0, 0, 0, 0, self.stream),
                    "acx_bfs_bucket")
-        offsets = torch.cumsum(counts, 0) - counts
-        cursor = torch.zeros((world,), dtype=torch.int64, device=d)
-        _lib.check(self.L.acx_bfs_bucket(_ptr(ch), _ptr(ln), _ptr(st), _ptr(po), n, self.m, world, _ptr(own), _ptr(counts),
+        offsets = torch.cumsum(counts[:G], 0) - counts[:G]
+        cursor = torch.zeros((G,), dtype=torch.int64, device=d)
+        _lib.check(self.L.acx_bfs_bucket(_ptr(ch), _ptr(ln), _ptr(st), _ptr(po), n, self.m, G, _ptr(own), _ptr(counts),
                                          _ptr(offsets), _ptr(cursor), _ptr(send), 1, self.stream), "acx_bfs_bucket")
-        return send, counts
+        self._packed = send
+        return counts
 
-    def probe(self, recv, n_parents):
-        n = recv.shape[0]
-        slot = torch.empty((n,), dtype=torch.int64, device=self.dev)
+    def deliver(self, allc, k):
+        """allc[s][o] = records rank s staged for owner o.  After this call the records this rank owns are in
+        self._recv as len(self._regions) regions of self._rcap_now records."""
+        G, rank = self.world, self.rank
+        scl = allc[rank][:G]
+        rcl = [allc[g][rank] for g in range(G)]
+        if self.transport == "p2p":  # already here: the senders' kernels wrote them
+            self._recv, self._regions, self._rcap_now = self.recv_bufs[k % 2], rcl, self.rcap
+            return
+        if self._packed is not None or not self.fused:
+            send = self._packed if self._packed is not None else torch.empty((0, self.rec), dtype=torch.uint8, device=self.dev)
+            starts = [sum(scl[:g]) for g in range(G)]
+        else:
+            send, starts = self.send, [g * self.rcap for g in range(G)]
+        if G == 1:
+            self._recv, self._regions, self._rcap_now = send[starts[0]:starts[0] + scl[0]], [scl[0]], max(scl[0], 1)
+            return
+        recv = torch.empty((sum(rcl), self.rec), dtype=torch.uint8, device=self.dev)
+        dist.all_to_all(list(recv.split(rcl)), [send[starts[g]:starts[g] + scl[g]] for g in range(G)], group=self._group)
+        self._recv, self._regions, self._rcap_now = recv, [sum(rcl)], max(sum(rcl), 1)
+
+    def _region_args(self):
+        import ctypes
+
+        return (ctypes.c_int64 * len(self._regions))(*self._regions), len(self._regions), self._rcap_now
+
+    def probe(self, n_parents):
+        rc, nreg, rcap = self._region_args()
+        self._slot = torch.empty((nreg * rcap,), dtype=torch.int64, device=self.dev)
         mask = torch.zeros((n_parents,), dtype=torch.int32, device=self.dev)
         mins = torch.full((2,), -1, dtype=torch.int64, device=self.dev)
-        if n:
-            _lib.check(self.L.acx_bfs_probe_packed(_ptr(recv), n, self.m, _ptr(self.table), self.tcap, _ptr(self.nodes), _ptr(slot),
-                                                   _ptr(mins), _ptr(mask), self.stream), "acx_bfs_probe_packed")
+        if sum(self._regions):
+            _lib.check(self.L.acx_bfs_probe_packed(_ptr(self._recv), rc, nreg, rcap, self.m, _ptr(self.table), self.tcap,
+                                                   _ptr(self.nodes), _ptr(self._slot), _ptr(mins), _ptr(mask), self.stream),
+                       "acx_bfs_probe_packed")
         mins = torch.where(mins < 0, torch.full_like(mins, SENT), mins)
-        return slot, mask, mins
+        return mask, mins
 
-    def commit(self, recv, slot, excl_par, gmask, parent_base, gid_base):
-        n = recv.shape[0]
-        if n:
-            _lib.check(self.L.acx_bfs_commit_packed(_ptr(recv), n, self.m, _ptr(slot), _ptr(excl_par), _ptr(gmask), parent_base,
-                                                    gid_base, _ptr(self.n_local_dev), _ptr(self.table), _ptr(self.nodes),
-                                                    _ptr(self.gid), _ptr(self.parent), _ptr(self.action), self.total.data_ptr(),
-                                                    self.stream), "acx_bfs_commit_packed")
+    def commit(self, excl_par, gmask, parent_base, gid_base):
+        rc, nreg, rcap = self._region_args()
+        if sum(self._regions):
+            _lib.check(self.L.acx_bfs_commit_packed(_ptr(self._recv), rc, nreg, rcap, self.m, _ptr(self._slot), _ptr(excl_par),
+                                                    _ptr(gmask), parent_base, gid_base, _ptr(self.n_local_dev), _ptr(self.table),
+                                                    _ptr(self.nodes), _ptr(self.gid), _ptr(self.parent), _ptr(self.action),
+                                                    self.total.data_ptr(), self.stream), "acx_bfs_commit_packed")
 
 
 class ShardedBFS:
@@ -146,7 +265,8 @@ class ShardedBFS:
         self.chunk = int(chunk)
         self.dev = shard.dev
         self.n_nodes, self.n_expanded, self.levels = 1, 0, []
-        self.comm_bytes = 0
+        self.comm_bytes, self.rounds = 0, 0
+        shard.connect(group)
         self.timers = None  # set to {} to collect a per-phase wall-clock breakdown (adds a device sync per phase)
         self._t0 = 0.0
 
@@ -159,6 +279,21 @@ class ShardedBFS:
         if name is not None:
             self.timers[name] = self.timers.get(name, 0.0) + now - self._t0
         self._t0 = now
+
+    def _exchange(self, counts, k):
+        """every rank learns how many records each rank staged for each owner (this all-gather is also the barrier
+        behind which the peer stores of the round are complete), then the shard takes delivery."""
+        G = self.world
+        if G == 1:
+            allc = [counts.tolist()]
+        else:
+            allc = torch.empty((G * (G + 1),), dtype=torch.int64, device=self.dev)
+            dist.all_gather_into_tensor(allc, counts, group=self.group)
+            allc = allc.view(G, G + 1).tolist()
+        if any(row[G] for row in allc):
+            raise RuntimeError("sharded bfs: a send region overflowed (hash imbalance above the 15% head room)")
+        self.shard.deliver(allc, k)
+        return self.shard.rec * (sum(allc[self.rank][:G]) - allc[self.rank][self.rank])
 
     def _lookup(self, gid):
         """(parent gid, action, total) of node `gid`, from whichever rank owns it"""
@@ -199,20 +334,16 @@ class ShardedBFS:
             for k, off in enumerate(range(lo, hi, self.chunk)):
                 C = min(self.chunk, hi - off)
                 a, b = cuts[k], cuts[k + 1]
-                rows = s.nodes[loc[a:b]]
-                send, counts = s.bucket(rows, gids[a:b] - off, G)
+                counts = s.stage(loc[a:b], gids[a:b], off, self.rounds)
                 self._tick("expand_bucket")
-                rc = torch.empty_like(counts)
-                dist.all_to_all_single(rc, counts, group=self.group)
-                rcl, scl = [int(v) for v in rc.tolist()], [int(v) for v in counts.tolist()]
-                recv = torch.empty((sum(rcl), send.shape[1]), dtype=torch.uint8, device=dev)
-                dist.all_to_all_single(recv, send, output_split_sizes=rcl, input_split_sizes=scl, group=self.group)
-                self.comm_bytes += send.shape[1] * (send.shape[0] - scl[self.rank])
+                self.comm_bytes += self._exchange(counts, self.rounds)
+                self.rounds += 1
                 self._tick("all_to_all")
-                slot, mask, mins = s.probe(recv, C)
+                mask, mins = s.probe(C)
                 self._tick("probe")
-                dist.all_reduce(mask, group=self.group)
-                dist.all_reduce(mins, op=dist.ReduceOp.MIN, group=self.group)
+                if G > 1:
+                    dist.all_reduce(mask, group=self.group)
+                    dist.all_reduce(mins, op=dist.ReduceOp.MIN, group=self.group)
                 cnt = popcount_lut(mask)
                 cum = torch.cumsum(cnt, dim=0)
                 c_s, c_e, n_new = torch.cat([mins, cum[-1:]]).tolist()
@@ -240,7 +371,7 @@ class ShardedBFS:
                     self.n_expanded += p_star + 1
                     self.n_nodes += int(cum[p_star])
                     return False, None
-                s.commit(recv, slot, cum - cnt, mask, off, self.n_nodes)
+                s.commit(cum - cnt, mask, off, self.n_nodes)
                 self._tick("commit")
                 self.n_nodes += n_new
                 self.n_expanded += C

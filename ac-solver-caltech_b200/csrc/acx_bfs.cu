@@ -16,12 +16,16 @@
 // Key equality is always decided by a full row compare; the tag only filters.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "../../include/acx.h"
 #include "acx_common.h"
+#include "acx_rows.cuh"
+#include "acx_expand_warp.cuh"
 
 namespace acx {
 
+static constexpr int ACX_BFS_MAX_WORLD = 32;
 static constexpr uint64_t PROV_BIT = 1ull << 47;
 static constexpr uint64_t VAL_MASK = PROV_BIT - 1;
 
@@ -243,12 +247,15 @@ __global__ void k_bfs_bucket_scatter(const int8_t* cand, const uint8_t* lens, co
     if (off != rowb) d4[rowb / 4] = 0u;
     *reinterpret_cast<int64_t*>(dst + off) = parent_ord[j / 12] * 12 + (j % 12);
     *reinterpret_cast<uint32_t*>(dst + off + 8) = (uint32_t)lens[2 * j] | ((uint32_t)lens[2 * j + 1] << 8) | ((uint32_t)status[j] << 16);
-    *reinterpret_cast<uint32_t*>(dst + off + 12) = 0u;
+    for (int k = off + 12; k < rec; k += 4) *reinterpret_cast<uint32_t*>(dst + k) = 0u;
 }
 
 struct PackedParams {
-    const uint8_t* recs;  // [n, rec]
-    int64_t n;
+    const uint8_t* recs;  // nreg regions of rcap records each; region s holds pre[s+1] - pre[s] records
+    int64_t n;            // records in all regions
+    int nreg;
+    int64_t rcap;
+    int64_t pre[ACX_BFS_MAX_WORLD + 1];
     int rowb, rec;
     uint64_t* table;
     int64_t tcap;
@@ -268,13 +275,21 @@ struct PackedParams {
     uint16_t* total;
 };
 
+// linear thread index -> record index (regions are filled from their start, with a gap behind each)
+__device__ __forceinline__ int64_t packed_index(const PackedParams& p, int64_t t) {
+    int s = 0;
+    while (s + 1 < p.nreg && t >= p.pre[s + 1]) ++s;
+    return (int64_t)s * p.rcap + (t - p.pre[s]);
+}
+
 __device__ __forceinline__ int64_t rec_order(const PackedParams& p, int64_t j) {
     return *reinterpret_cast<const int64_t*>(p.recs + j * p.rec + (p.rowb + 7) / 8 * 8);
 }
 
 __global__ void k_bfs_probe_packed(const PackedParams p) {
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= p.n) return;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.n) return;
+    const int64_t j = packed_index(p, t);
     const int nwords = p.rowb / 4, off = (p.rowb + 7) / 8 * 8;
     const uint8_t* rec = p.recs + j * p.rec;
     const uint32_t* row = reinterpret_cast<const uint32_t*>(rec);
@@ -341,8 +356,9 @@ __global__ void k_bfs_probe_packed(const PackedParams p) {
 
 // new candidates set their bit in the per-parent mask of the round
 __global__ void k_bfs_resolve_packed(const PackedParams p) {
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= p.n) return;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.n) return;
+    const int64_t j = packed_index(p, t);
     const int64_t s = p.slot[j];
     if (s < 0) return;
     const uint64_t e = p.table[s];
@@ -356,8 +372,9 @@ __global__ void k_bfs_resolve_packed(const PackedParams p) {
 
 // new candidates become local nodes; their global id follows from the all-reduced masks
 __global__ void k_bfs_commit_packed(const PackedParams p) {
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= p.n) return;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.n) return;
+    const int64_t j = packed_index(p, t);
     const int64_t s = p.slot[j];
     if (s < 0) return;
     const int off = (p.rowb + 7) / 8 * 8;
@@ -377,6 +394,188 @@ __global__ void k_bfs_commit_packed(const PackedParams p) {
     p.total[id] = (uint16_t)((meta & 0xFFu) + ((meta >> 8) & 0xFFu));
     const uint64_t e = p.table[s];
     p.table[s] = (e & ~(PROV_BIT | VAL_MASK)) | (uint64_t)id;
+}
+
+// Fused frontier step of the sharded bfs: gather 32 parents per warp by index, apply the 12 moves on bit planes
+// (same row code as k_expand_warp), build the packed record of every child in shared memory, hash it, pick its
+// owner rank and copy the record straight into that owner's region of the send buffer.  Slots are reserved per
+// warp and per group of GM moves: one ballot scan per owner, one atomicAdd per owner per warp-step.
+// send = [world][region_cap] records; cursor[o] = records written to region o; cursor[world] = overflow flag.
+struct BucketDst {
+    uint8_t* region[ACX_BFS_MAX_WORLD];  // this sender's region in the receive buffer of each owner (local or peer memory)
+};
+
+template <int MS, int GM, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) k_bfs_expand_bucket(const int8_t* nodes, const int64_t* loc, const int64_t* gids,
+                                                                  int64_t ord_base, int64_t f, int cyclical, int world,
+                                                                  int64_t region_cap, unsigned long long* cursor,
+                                                                  const BucketDst dst, int64_t ntiles) {
+    using Ops = PlaneOps<2, MS>;
+    using R = R64;
+    constexpr int ROWB = 2 * MS, REC = (ROWB + 16 + 15) / 16 * 16, PCH = ROWB / 8, RCH = REC / 16;
+    static_assert(ROWB % 8 == 0, "rows must be whole 8-byte words");
+    // records are whole 32-byte sectors (96 B at m = 36) and leave in 16-byte stores: full-sector writes over NVLink
+    constexpr int CSTRIDE = GM * REC + 8;  // CSTRIDE / 8 odd: conflict-free 64-bit accesses across lanes
+    constexpr int WARP_BYTES = 32 * (2 * ROWB + CSTRIDE) + 32 * GM * 4;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint8_t* par = smem + (size_t)wid * WARP_BYTES;
+    uint8_t* base = par + 32 * ROWB;
+    uint8_t* cbuf = base + 32 * ROWB;
+    uint32_t* spos = reinterpret_cast<uint32_t*>(cbuf + 32 * CSTRIDE);
+    const bool cyc = cyclical != 0;
+    const unsigned ltmask = (1u << lane) - 1u;
+    const int64_t warp0 = (int64_t)blockIdx.x * WARPS + wid, nwarps = (int64_t)gridDim.x * WARPS;
+    const uint8_t* gn = reinterpret_cast<const uint8_t*>(nodes);
+
+    for (int64_t tile = warp0; tile < ntiles; tile += nwarps) {
+        const int64_t f0 = tile * 32;
+        const int nrows = (int)min((int64_t)32, f - f0);
+        for (int c = lane; c < nrows * PCH; c += 32) {
+            const int pr = c / PCH, o = c - pr * PCH;
+            *reinterpret_cast<uint2*>(par + pr * ROWB + o * 8) =
+                *reinterpret_cast<const uint2*>(gn + loc[f0 + pr] * (int64_t)ROWB + o * 8);
+        }
+        __syncwarp();
+        const bool active = lane < nrows;
+        const int64_t ord0 = active ? (gids[f0 + lane] - ord_base) * 12 : 0;
+        uint8_t* prow = par + lane * ROWB;
+        uint8_t* brow = base + lane * ROWB;
+        R r[2], rc[2];
+        int cnt[2] = {0, 0};
+        int cls = ROW_INVALID;
+        if (active) cls = Ops::classify(prow, r, cnt);
+        const bool fast = active && cls == ROW_FAST;
+        if (fast) {
+            for (int k = 0; k < PCH; ++k) reinterpret_cast<uint2*>(brow)[k] = reinterpret_cast<const uint2*>(prow)[k];
+            rc[0] = r[0];
+            rc[1] = r[1];
+            if (cyc) {
+                Ops::cyclic(rc[0]);
+                Ops::cyclic(rc[1]);
+                if (rc[0].n != r[0].n) Ops::unpack(brow, rc[0]);
+                if (rc[1].n != r[1].n) Ops::unpack(brow + MS, rc[1]);
+            }
+        }
+#pragma unroll 1
+        for (int g = 0; g < 12 / GM; ++g) {
+            int own[GM];
+            unsigned rank[GM];
+#pragma unroll
+            for (int j = 0; j < GM; ++j) {
+                const int a = g * GM + j;
+                uint8_t* child = cbuf + lane * CSTRIDE + j * REC;
+                own[j] = -1;
+                rank[j] = 0;
+                if (!active) continue;
+                int l0 = cnt[0], l1 = cnt[1];
+                uint32_t st = ACX_ROW_OK;
+                bool moved = true;
+                if (fast) {
+                    const uint32_t d = decode_move(a);
+                    const bool i = d & 1u, is_conj = d & 2u, inv = d & 4u;
+                    R x = Ops::select(i, r[0], r[1]);
+                    bool changed;
+                    if (!is_conj) {
+                        R b = Ops::select(!i, r[0], r[1]);
+                        if (inv) b = Ops::inverse(b);
+                        changed = Ops::concat(x, b);
+                    } else {
+                        changed = Ops::conjugate(x, inv ? 1u : 0u, (d >> 3) & 1u);
+                    }
+                    moved = changed;
+                    if (x.n == 0) {
+                        st = ACX_ROW_EMPTY_RELATOR;
+                        for (int k = 0; k < PCH; ++k) reinterpret_cast<uint2*>(child)[k] = reinterpret_cast<const uint2*>(prow)[k];
+                    } else {
+                        for (int k = 0; k < PCH; ++k) reinterpret_cast<uint2*>(child)[k] = reinterpret_cast<const uint2*>(brow)[k];
+                        if (changed) {
+                            if (cyc) Ops::cyclic(x);
+                            Ops::unpack(child + (d & 1u) * MS, x);
+                        }
+                        const int na = changed ? x.n : (i ? rc[1].n : rc[0].n);
+                        l0 = i ? rc[0].n : na;
+                        l1 = i ? na : rc[1].n;
+                    }
+                } else {
+                    for (int k = 0; k < PCH; ++k) reinterpret_cast<uint2*>(child)[k] = reinterpret_cast<const uint2*>(prow)[k];
+                    acmove_row64<MS>(child, MS, a, cyc, l0, l1, st);
+                }
+                // a move that leaves the presentation untouched (e.g. the product would exceed max_relator_length)
+                // reproduces the parent, which is already in the visited set: nothing to send
+                if (fast && st == ACX_ROW_OK && !moved && rc[0].n == r[0].n && rc[1].n == r[1].n) continue;
+                *reinterpret_cast<int64_t*>(child + ROWB) = ord0 + a;
+                *reinterpret_cast<uint2*>(child + ROWB + 8) = make_uint2((uint32_t)l0 | ((uint32_t)l1 << 8) | (st << 16), 0u);
+                for (int k = ROWB + 16; k < REC; k += 8) *reinterpret_cast<uint2*>(child + k) = make_uint2(0u, 0u);
+                own[j] = bfs_owner(bfs_row_hash(reinterpret_cast<const uint32_t*>(child), ROWB / 4), world);
+            }
+            // slots: per owner, rank of each child among the warp-step's children of that owner
+            unsigned mycnt = 0;
+            for (int o = 0; o < world; ++o) {
+                unsigned run = 0;
+#pragma unroll
+                for (int j = 0; j < GM; ++j) {
+                    const unsigned b = __ballot_sync(0xFFFFFFFFu, own[j] == o);
+                    if (own[j] == o) rank[j] = run + __popc(b & ltmask);
+                    run += __popc(b);
+                }
+                if (lane == o) mycnt = run;
+            }
+            unsigned long long mybase = 0;
+            if (lane < world && mycnt) mybase = atomicAdd(cursor + lane, (unsigned long long)mycnt);
+#pragma unroll
+            for (int j = 0; j < GM; ++j) {
+                const unsigned long long b = __shfl_sync(0xFFFFFFFFu, mybase, own[j] < 0 ? 0 : own[j]);
+                uint32_t idx = 0xFFFFFFFFu;
+                if (own[j] >= 0) {
+                    const unsigned long long pos = b + rank[j];
+                    if (pos < (unsigned long long)region_cap) idx = ((uint32_t)own[j] << 27) | (uint32_t)pos;
+                    else cursor[world] = 1ull;  // a region overflowed: the host raises
+                }
+                spos[lane * GM + j] = idx;
+            }
+            __syncwarp();
+            for (int it = lane; it < nrows * GM * RCH; it += 32) {
+                const int c = it / RCH, k = it - c * RCH;
+                const int pr = c / GM, j = c - pr * GM;
+                const uint32_t idx = spos[c];
+                if (idx != 0xFFFFFFFFu) {  // local or NVLink peer store
+                    const uint2* src = reinterpret_cast<const uint2*>(cbuf + pr * CSTRIDE + j * REC + 16 * k);
+                    const uint2 lo = src[0], hi = src[1];
+                    *reinterpret_cast<uint4*>(dst.region[idx >> 27] + (size_t)(idx & 0x7FFFFFFu) * REC + 16 * k) =
+                        make_uint4(lo.x, lo.y, hi.x, hi.y);
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+template <int MS, int GM, int WARPS>
+static int launch_expand_bucket(const int8_t* nodes, const int64_t* loc, const int64_t* gids, int64_t ord_base, int64_t f,
+                                int cyclical, int world, int64_t region_cap, uint64_t* cursor, const BucketDst& dst,
+                                cudaStream_t st) {
+    constexpr int ROWB = 2 * MS, REC = (ROWB + 16 + 15) / 16 * 16, CSTRIDE = GM * REC + 8;
+    constexpr size_t smem = (size_t)WARPS * (32 * (2 * ROWB + CSTRIDE) + 32 * GM * 4);
+    auto kern = k_bfs_expand_bucket<MS, GM, WARPS>;
+    static int ctas_per_sm[ACX_MAX_DEVICES] = {0};
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= ACX_MAX_DEVICES) dev = 0;
+    if (ctas_per_sm[dev] == 0) {
+        ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 0;
+        ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * WARPS, smem));
+        ctas_per_sm[dev] = occ > 0 ? occ : 1;
+    }
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t ntiles = (f + 31) / 32;
+    int64_t grid = (ntiles + WARPS - 1) / WARPS;
+    if (grid > (int64_t)sms * ctas_per_sm[dev]) grid = (int64_t)sms * ctas_per_sm[dev];
+    kern<<<(unsigned)grid, 32 * WARPS, smem, st>>>(nodes, loc, gids, ord_base, f, cyclical, world, region_cap,
+                                                   reinterpret_cast<unsigned long long*>(cursor), dst, ntiles);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
 }
 
 }  // namespace acx
@@ -434,7 +633,7 @@ extern "C" int acx_rows_hash(const int8_t* rows, int64_t n, int m, uint64_t* has
     return ACX_OK;
 }
 
-extern "C" int acx_bfs_record_bytes(int m) { return (2 * m + 7) / 8 * 8 + 16; }
+extern "C" int acx_bfs_record_bytes(int m) { return ((2 * m + 7) / 8 * 8 + 16 + 15) / 16 * 16; }
 
 extern "C" int acx_bfs_bucket(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* parent_ord,
                               int64_t n, int m, int world, uint8_t* owner_scratch, uint64_t* counts, int64_t* offsets,
@@ -455,34 +654,98 @@ extern "C" int acx_bfs_bucket(const int8_t* cand, const uint8_t* lens, const uin
     return ACX_OK;
 }
 
-extern "C" int acx_bfs_probe_packed(const uint8_t* recs, int64_t n, int m, uint64_t* table, int64_t tcap, const int8_t* nodes,
-                                    int64_t* slot, uint64_t* mins, int32_t* mask, acx_stream_t stream) {
-    if (n < 0 || m < 1 || (2 * m) % 4 != 0 || tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe_packed: bad argument");
-    if (n == 0) return ACX_OK;
-    if (!recs || !table || !nodes || !slot || !mins || !mask) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe_packed: null pointer");
+static int fill_regions(PackedParams& p, const int64_t* region_counts, int n_regions, int64_t region_cap, const char* who) {
+    if (!region_counts || n_regions < 1 || n_regions > ACX_BFS_MAX_WORLD || region_cap < 0)
+        return acx_fail(ACX_ERR_ARG, "%s: need 1 <= n_regions <= 32 and a host array of region counts", who);
+    p.nreg = n_regions;
+    p.rcap = region_cap;
+    p.pre[0] = 0;
+    for (int s = 0; s < n_regions; ++s) {
+        if (region_counts[s] < 0 || region_counts[s] > region_cap) return acx_fail(ACX_ERR_ARG, "%s: region count out of range", who);
+        p.pre[s + 1] = p.pre[s] + region_counts[s];
+    }
+    p.n = p.pre[n_regions];
+    return ACX_OK;
+}
+
+extern "C" int acx_bfs_probe_packed(const uint8_t* recs, const int64_t* region_counts, int n_regions, int64_t region_cap, int m,
+                                    uint64_t* table, int64_t tcap, const int8_t* nodes, int64_t* slot, uint64_t* mins,
+                                    int32_t* mask, acx_stream_t stream) {
+    if (m < 1 || (2 * m) % 4 != 0 || tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe_packed: bad argument");
     PackedParams p = {};
-    p.recs = recs; p.n = n; p.rowb = 2 * m; p.rec = acx_bfs_record_bytes(m); p.table = table; p.tcap = tcap; p.nodes = nodes;
+    if (int rc = fill_regions(p, region_counts, n_regions, region_cap, "acx_bfs_probe_packed")) return rc;
+    if (p.n == 0) return ACX_OK;
+    if (!recs || !table || !nodes || !slot || !mins || !mask) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe_packed: null pointer");
+    p.recs = recs; p.rowb = 2 * m; p.rec = acx_bfs_record_bytes(m); p.table = table; p.tcap = tcap; p.nodes = nodes;
     p.slot = slot; p.mins = reinterpret_cast<unsigned long long*>(mins); p.mask = mask;
-    const unsigned grid = (unsigned)((n + 255) / 256);
+    const unsigned grid = (unsigned)((p.n + 255) / 256);
     k_bfs_probe_packed<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     k_bfs_resolve_packed<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }
 
-extern "C" int acx_bfs_commit_packed(const uint8_t* recs, int64_t n, int m, const int64_t* slot, const int64_t* excl_par,
-                                     const int32_t* gmask, int64_t parent_base, int64_t gid_base, uint64_t* n_local,
-                                     uint64_t* table, int8_t* nodes, int64_t* gid, int64_t* parent, uint8_t* action,
-                                     uint16_t* total, acx_stream_t stream) {
-    if (n < 0 || m < 1 || (2 * m) % 4 != 0) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit_packed: bad argument");
-    if (n == 0) return ACX_OK;
-    if (!recs || !slot || !excl_par || !gmask || !n_local || !table || !nodes || !gid || !parent || !action || !total) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit_packed: null pointer");
+extern "C" int acx_bfs_commit_packed(const uint8_t* recs, const int64_t* region_counts, int n_regions, int64_t region_cap, int m,
+                                     const int64_t* slot, const int64_t* excl_par, const int32_t* gmask, int64_t parent_base,
+                                     int64_t gid_base, uint64_t* n_local, uint64_t* table, int8_t* nodes, int64_t* gid,
+                                     int64_t* parent, uint8_t* action, uint16_t* total, acx_stream_t stream) {
+    if (m < 1 || (2 * m) % 4 != 0) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit_packed: bad argument");
     PackedParams p = {};
-    p.recs = recs; p.n = n; p.rowb = 2 * m; p.rec = acx_bfs_record_bytes(m); p.table = table; p.slot = const_cast<int64_t*>(slot);
+    if (int rc = fill_regions(p, region_counts, n_regions, region_cap, "acx_bfs_commit_packed")) return rc;
+    if (p.n == 0) return ACX_OK;
+    if (!recs || !slot || !excl_par || !gmask || !n_local || !table || !nodes || !gid || !parent || !action || !total) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit_packed: null pointer");
+    p.recs = recs; p.rowb = 2 * m; p.rec = acx_bfs_record_bytes(m); p.table = table; p.slot = const_cast<int64_t*>(slot);
     p.excl_par = excl_par; p.gmask = gmask; p.parent_base = parent_base; p.gid_base = gid_base;
     p.n_local = reinterpret_cast<unsigned long long*>(n_local); p.nodes_w = nodes; p.gid = gid; p.parent = parent; p.action = action;
     p.total = total;
-    k_bfs_commit_packed<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
+    k_bfs_commit_packed<<<(unsigned)((p.n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+extern "C" int acx_bfs_expand_bucket(const int8_t* nodes, const int64_t* loc, const int64_t* gids, int64_t ord_base, int64_t f,
+                                     int m, int cyclical, int world, int64_t region_cap, uint64_t* cursor,
+                                     uint8_t* const* dst_regions, acx_stream_t stream) {
+    if (f < 0 || world < 1 || world > ACX_BFS_MAX_WORLD || region_cap < 1 || region_cap >= (1ll << 27))
+        return acx_fail(ACX_ERR_ARG, "acx_bfs_expand_bucket: bad argument (1 <= world <= 32, region_cap < 2^27)");
+    if (m != 36) return acx_fail(ACX_ERR_ARG, "acx_bfs_expand_bucket: built for max_relator_length 36 (use acx_expand12 + acx_bfs_bucket otherwise)");
+    if (f == 0) return ACX_OK;
+    if (!nodes || !loc || !gids || !cursor || !dst_regions) return acx_fail(ACX_ERR_ARG, "acx_bfs_expand_bucket: null pointer");
+    BucketDst dst = {};
+    for (int o = 0; o < world; ++o) {
+        if (!dst_regions[o] || ((uintptr_t)dst_regions[o] & 15u)) return acx_fail(ACX_ERR_ARG, "acx_bfs_expand_bucket: destination regions must be non-null and 16-byte aligned");
+        dst.region[o] = dst_regions[o];
+    }
+    if ((uintptr_t)nodes & 7u) return acx_fail(ACX_ERR_ARG, "acx_bfs_expand_bucket: nodes must be 8-byte aligned");
+    return launch_expand_bucket<36, 4, 4>(nodes, loc, gids, ord_base, f, cyclical, world, region_cap, cursor, dst, (cudaStream_t)stream);
+}
+
+// Peer memory: buffers another process on the same NVLink domain may write into (CUDA IPC).
+extern "C" int acx_peer_alloc(int64_t bytes, void** ptr) {
+    if (bytes <= 0 || !ptr) return acx_fail(ACX_ERR_ARG, "acx_peer_alloc: bad argument");
+    ACX_CUDA(cudaMalloc(ptr, (size_t)bytes));
+    return ACX_OK;
+}
+extern "C" int acx_peer_free(void* ptr) {
+    if (ptr) ACX_CUDA(cudaFree(ptr));
+    return ACX_OK;
+}
+extern "C" int acx_peer_export(const void* ptr, uint8_t* handle64) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    if (!ptr || !handle64) return acx_fail(ACX_ERR_ARG, "acx_peer_export: null pointer");
+    cudaIpcMemHandle_t h;
+    ACX_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
+    memcpy(handle64, &h, 64);
+    return ACX_OK;
+}
+extern "C" int acx_peer_open(const uint8_t* handle64, void** ptr) {
+    if (!ptr || !handle64) return acx_fail(ACX_ERR_ARG, "acx_peer_open: null pointer");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    ACX_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return ACX_OK;
+}
+extern "C" int acx_peer_close(void* ptr) {
+    if (ptr) ACX_CUDA(cudaIpcCloseMemHandle(ptr));
     return ACX_OK;
 }

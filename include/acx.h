@@ -143,24 +143,46 @@ int acx_bfs_commit(const int8_t* cand, const uint8_t* lens, const int64_t* slot,
 int acx_rows_hash(const int8_t* rows, int64_t n, int m, uint64_t* hash_out, acx_stream_t stream);
 
 /* Hash-partitioned (multi-GPU) bfs: candidates travel to their owner rank as packed records
- *     row (2m bytes, padded to 8) | int64 order | uint8 len0 | uint8 len1 | uint8 status | pad   (acx_bfs_record_bytes)
+ *     row (2m bytes, padded to 8) | int64 order | uint8 len0 | uint8 len1 | uint8 status | pad to 16   (acx_bfs_record_bytes)
  * with owner(state) = ((hash >> 20) & 0x7fffffff) % world.
  *   acx_bfs_bucket        phase 0: owner of each candidate + per-owner counts; phase 1: scatter the records into
  *                         `send`, grouped by owner at offsets[] (exclusive scan of counts), ready for the all-to-all-v.
  *                         order of candidate j = parent_ord[j / 12] * 12 + j % 12.
  *   acx_bfs_probe_packed  acx_bfs_probe on received records; new candidates OR their bit into mask[order / 12].
  *   acx_bfs_commit_packed new candidates become local nodes; global id = gid_base + excl_par[p] +
- *                         popcount(gmask[p] & bits below the action), from the all-reduced masks. */
+ *                         popcount(gmask[p] & bits below the action), from the all-reduced masks.
+ *   acx_bfs_expand_bucket the fused frontier step for max_relator_length 36: parents nodes[loc[k]] (k < f, global
+ *                         discovery ids gids[k]) -> 12 children each -> packed records written straight to
+ *                         dst_regions[owner] (host array of `world` device pointers, each a region of region_cap
+ *                         records: a local send buffer, or this rank's region inside the owner's peer receive
+ *                         buffer); cursor[o] counts region o, cursor[world] != 0 flags a region overflow.
+ *                         order of child (k, a) = (gids[k] - ord_base) * 12 + a.  Children equal to their parent
+ *                         are dropped (already visited).
+ *   probe/commit_packed take the records as n_regions regions of region_cap records, region s holding
+ *                         region_counts[s] (host array) records from its start; record index = s * region_cap + i.
+ */
 int acx_bfs_record_bytes(int m);
+int acx_bfs_expand_bucket(const int8_t* nodes, const int64_t* loc, const int64_t* gids, int64_t ord_base, int64_t f, int m,
+                          int cyclical, int world, int64_t region_cap, uint64_t* cursor, uint8_t* const* dst_regions,
+                          acx_stream_t stream);
 int acx_bfs_bucket(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* parent_ord, int64_t n,
                    int m, int world, uint8_t* owner_scratch, uint64_t* counts, int64_t* offsets, uint64_t* cursor,
                    uint8_t* send, int phase, acx_stream_t stream);
-int acx_bfs_probe_packed(const uint8_t* recs, int64_t n, int m, uint64_t* table, int64_t tcap, const int8_t* nodes,
-                         int64_t* slot, uint64_t* mins, int32_t* mask, acx_stream_t stream);
-int acx_bfs_commit_packed(const uint8_t* recs, int64_t n, int m, const int64_t* slot, const int64_t* excl_par,
-                          const int32_t* gmask, int64_t parent_base, int64_t gid_base, uint64_t* n_local, uint64_t* table,
-                          int8_t* nodes, int64_t* gid, int64_t* parent, uint8_t* action, uint16_t* total,
-                          acx_stream_t stream);
+int acx_bfs_probe_packed(const uint8_t* recs, const int64_t* region_counts, int n_regions, int64_t region_cap, int m,
+                         uint64_t* table, int64_t tcap, const int8_t* nodes, int64_t* slot, uint64_t* mins, int32_t* mask,
+                         acx_stream_t stream);
+int acx_bfs_commit_packed(const uint8_t* recs, const int64_t* region_counts, int n_regions, int64_t region_cap, int m,
+                          const int64_t* slot, const int64_t* excl_par, const int32_t* gmask, int64_t parent_base,
+                          int64_t gid_base, uint64_t* n_local, uint64_t* table, int8_t* nodes, int64_t* gid, int64_t* parent,
+                          uint8_t* action, uint16_t* total, acx_stream_t stream);
+
+/* Peer memory (CUDA IPC): a receive buffer the other ranks of one NVLink domain write into directly, so that
+ * acx_bfs_expand_bucket IS the all-to-all (stores over NVLink from inside the kernel, no staging, no collective). */
+int acx_peer_alloc(int64_t bytes, void** ptr);
+int acx_peer_free(void* ptr);
+int acx_peer_export(const void* ptr, uint8_t* handle64);
+int acx_peer_open(const uint8_t* handle64, void** ptr);
+int acx_peer_close(void* ptr);
 
 #ifdef __cplusplus
 }

@@ -19,7 +19,7 @@ class OracleShard:
         self.action = torch.zeros((cap_local,), dtype=torch.uint8)
         self.total = torch.zeros((cap_local,), dtype=torch.int16)
         self._n = 0
-        self.rec = (self.rowb + 7) // 8 * 8 + 16
+        self.rec = ((self.rowb + 7) // 8 * 8 + 16 + 15) // 16 * 16
         self.table = {}  # row bytes -> ("node", idx) | ("cand", j)
 
     def seed(self, root):
@@ -44,12 +44,19 @@ class OracleShard:
     def owner_of_row(self, row, world):
         return int(((self._hash(np.ascontiguousarray(row[None, :])) >> np.uint64(20)) & np.uint64(0x7FFFFFFF))[0] % world)
 
-    def bucket(self, rows, parent_ord, world):
+    def connect(self, group=None):
+        import torch.distributed as dist
+
+        self._group, self.world, self.rank = group, dist.get_world_size(group), dist.get_rank(group)
+
+    def stage(self, loc, gids, ord_base, k):
+        world = self.world
+        rows, parent_ord = self.nodes[loc], gids - ord_base
         f = rows.shape[0]
         n = 12 * f
         off = (self.rowb + 7) // 8 * 8
         send = np.zeros((n, self.rec), dtype=np.uint8)
-        counts = np.zeros(world, dtype=np.int64)
+        counts = np.zeros(world + 1, dtype=np.int64)
         if f:
             ch, ln, st = ac_oracle.expand12_batch(rows.numpy(), cyclical=self.cyc)
             ch = np.ascontiguousarray(ch.reshape(n, self.rowb))
@@ -63,8 +70,18 @@ class OracleShard:
             # any order inside an owner group is legal: scramble it to prove the receiver does not depend on it
             perm = np.lexsort((np.random.default_rng(n).permutation(n), own))
             send = rec[perm]
-            counts = np.bincount(own.astype(np.int64), minlength=world).astype(np.int64)
-        return torch.from_numpy(send), torch.from_numpy(counts)
+            counts[:world] = np.bincount(own.astype(np.int64), minlength=world)
+        self._send = torch.from_numpy(send)
+        return torch.from_numpy(counts)
+
+    def deliver(self, allc, k):
+        import torch.distributed as dist
+
+        G = self.world
+        scl, rcl = allc[self.rank][:G], [allc[g][self.rank] for g in range(G)]
+        recv = torch.empty((sum(rcl), self.rec), dtype=torch.uint8)
+        dist.all_to_all_single(recv, self._send, output_split_sizes=rcl, input_split_sizes=scl, group=self._group)
+        self._recv = recv
 
     def _fields(self, recv):
         r = recv.numpy()
@@ -73,7 +90,8 @@ class OracleShard:
         order = np.ascontiguousarray(r[:, off:off + 8]).view(np.int64).reshape(-1)
         return rows, order, r[:, off + 8:off + 10], r[:, off + 10]
 
-    def probe(self, recv, n_parents):
+    def probe(self, n_parents):
+        recv = self._recv
         n = recv.shape[0]
         c, o, l, s = self._fields(recv)
         slot = torch.full((n,), -1, dtype=torch.int64)
@@ -95,10 +113,11 @@ class OracleShard:
             if keys[j] is not None and self.table[keys[j]] == ("cand", j):
                 slot[j] = 0
                 mask[int(o[j]) // 12] |= 1 << (int(o[j]) % 12)
-        self._keys = keys
-        return slot, mask, torch.tensor(mins, dtype=torch.int64)
+        self._keys, self._slot = keys, slot
+        return mask, torch.tensor(mins, dtype=torch.int64)
 
-    def commit(self, recv, slot, excl_par, gmask, parent_base, gid_base):
+    def commit(self, excl_par, gmask, parent_base, gid_base):
+        recv, slot = self._recv, self._slot
         c, o, l, s = self._fields(recv)
         for j in range(recv.shape[0]):
             if slot[j] >= 0:

@@ -73,7 +73,7 @@ def test_sharded_bfs_single_rank_gpu(cuda, oracle, golden_dir):
             for budget, chunk in ((1, 4), (14, 4), (700, 64), (30000, 4096)):
                 cyc = bool(rng.integers(0, 2))
                 row = rows[int(k)]
-                shard = GpuShard(len(row) // 2, cyc, budget + 64, 12 * chunk, str(cuda))
+                shard = GpuShard(len(row) // 2, cyc, budget + 64, chunk, str(cuda))
                 eng = ShardedBFS(row, budget, shard, chunk=chunk)
                 ok, path = eng.run()
                 stats = {}

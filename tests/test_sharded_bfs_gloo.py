@@ -47,7 +47,17 @@ def test_sharded_bfs_world2_matches_oracle(oracle, golden_dir):
     procs = [ctx.Process(target=_worker, args=(r, 2, port, cases, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = dict(q.get(timeout=600) for _ in range(2))
+    got = {}
+    import queue as _queue
+    import time as _time
+    t_end = _time.time() + 600
+    while len(got) < 2:
+        try:
+            rank, res = q.get(timeout=2)
+            got[rank] = res
+        except _queue.Empty:
+            assert all(p.exitcode in (None, 0) for p in procs), "a rank died: %s" % [p.exitcode for p in procs]
+            assert _time.time() < t_end, "timed out"
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
