@@ -101,13 +101,13 @@ class GpuShard:
             return
         G, rank = dist.get_world_size(group), dist.get_rank(group)
         self.world, self.rank = G, rank
-        self.fused = self.m == 36 and G <= 32
+        self.fused = self._fusable(G)
         f = self.fmax
         self.rcap = 12 * f if G == 1 else min(12 * f, int(12 * f / G * 1.15) + 8192)
         if self.transport == "auto":
             self.transport = "p2p" if (self.fused and G > 1) else "nccl"
         if self.transport == "p2p" and not (self.fused and G > 1):
-            raise ValueError("transport 'p2p' needs max_relator_length 36 and 2..32 ranks")
+            raise ValueError("transport 'p2p' needs the fused expand kernel (max_relator_length 36 or plane nodes) and 2..32 ranks")
         nbytes = G * self.rcap * self.rec
         if self.transport == "p2p":
             import ctypes
@@ -140,6 +140,12 @@ class GpuShard:
             self.send = torch.empty((G * self.rcap, self.rec), dtype=torch.uint8, device=self.dev)
             self.dst = [[self.send.data_ptr() + g * self.rcap * self.rec for g in range(G)]] * 2
         self._group = group
+
+    def _fusable(self, world):
+        return self.m == 36 and world <= 32
+
+    def node_total(self, k):
+        return self.total[k].to(torch.int64)
 
     def close(self):
         """collective: nobody may still be writing into a peer buffer when it is unmapped / freed"""
@@ -255,6 +261,118 @@ class GpuShard:
                                                     self.total.data_ptr(), self.stream), "acx_bfs_commit_packed")
 
 
+class PlaneShard(GpuShard):
+    """The shard on bit-plane nodes (csrc/acx_pbfs.cu): a node / a candidate record is 32 bytes instead of 2m / 2m+24,
+    the moves run on the planes in registers and nothing is packed or unpacked on the way.  For max_relator_length
+    <= 36 and roots inside the plane domain (PlaneShard.accepts); same protocol and transports as GpuShard."""
+
+    def __init__(self, m, cyclical, cap_local, max_parents, device, transport="auto"):
+        if m > 36:
+            raise ValueError("plane nodes hold max_relator_length <= 36")
+        self.m, self.rowb, self.cyc = m, 2 * m, bool(cyclical)
+        self.rec = 32
+        self.dev = torch.device(device)
+        self.stream = _prep(self.dev)
+        d = self.dev
+        self.cap = int(cap_local)
+        self.fmax = int(max_parents)
+        self.tcap = _next_pow2(2 * (self.cap + 12 * self.fmax))
+        self.nodes = torch.zeros((self.cap, 4), dtype=torch.int64, device=d)
+        self.gid = torch.full((self.cap,), -1, dtype=torch.int64, device=d)
+        self.parent = torch.full((self.cap,), -1, dtype=torch.int64, device=d)
+        self.action = torch.zeros((self.cap,), dtype=torch.uint8, device=d)
+        self.table = torch.zeros((self.tcap,), dtype=torch.int64, device=d)
+        self.n_local_dev = torch.zeros((1,), dtype=torch.int64, device=d)
+        self.L = _lib.lib()
+        self.transport = transport
+        self._own, self._opened = [], []
+        self.world = None
+
+    def _fusable(self, world):
+        return world <= 32
+
+    def pack(self, rows):
+        """byte rows [n, 2m] (numpy) -> (plane nodes int64 [n, 4] on the device, ok uint8 [n])"""
+        r = torch.from_numpy(np.ascontiguousarray(rows, dtype=np.int8)).to(self.dev)
+        out = torch.empty((r.shape[0], 4), dtype=torch.int64, device=self.dev)
+        ok = torch.empty((r.shape[0],), dtype=torch.uint8, device=self.dev)
+        _lib.check(self.L.acx_pbfs_pack(_ptr(r), r.shape[0], self.m, int(self.cyc), _ptr(out), _ptr(ok), self.stream), "acx_pbfs_pack")
+        return out, ok
+
+    def unpack(self, nodes):
+        rows = torch.empty((nodes.shape[0], self.rowb), dtype=torch.int8, device=self.dev)
+        _lib.check(self.L.acx_pbfs_unpack(_ptr(nodes.contiguous()), nodes.shape[0], self.m, _ptr(rows), self.stream), "acx_pbfs_unpack")
+        return rows
+
+    def accepts(self, root):
+        """is the root inside the plane domain (letters +-1, +-2, freely reduced, cyclically reduced when cyclical)?"""
+        node, ok = self.pack(root[None, :])
+        self._root_node = node
+        return bool(ok[0])
+
+    def owner_of_row(self, row, world):
+        if not self.accepts(row):
+            raise ValueError("root outside the plane domain: use GpuShard")
+        h = torch.empty((1,), dtype=torch.int64, device=self.dev)
+        _lib.check(self.L.acx_pbfs_hash(_ptr(self._root_node), 1, _ptr(h), self.stream), "acx_pbfs_hash")
+        return int(owner_of(h, world)[0])
+
+    def seed(self, root):
+        self.nodes[0].copy_(self._root_node[0])
+        self.gid[0] = 0
+        _lib.check(self.L.acx_pbfs_seed(_ptr(self.nodes), _ptr(self.table), self.tcap, 0, self.stream), "acx_pbfs_seed")
+        self.n_local_dev.fill_(1)
+
+    def node_total(self, k):
+        w = self.nodes[k]
+        return ((w[0] >> 40) & 63) + ((w[1] >> 40) & 63)
+
+    def stage(self, loc, gids, ord_base, k):
+        import ctypes
+
+        G, f = self.world, loc.shape[0]
+        if f > self.fmax:
+            raise RuntimeError("sharded bfs: %d local parents in one round, buffers sized for %d" % (f, self.fmax))
+        counts = torch.zeros((G + 1,), dtype=torch.int64, device=self.dev)
+        self._packed = None
+        if f:
+            loc, gids = loc.contiguous(), gids.contiguous()
+            dst = (ctypes.c_void_p * G)(*self.dst[k % 2])
+            _lib.check(self.L.acx_pbfs_expand(_ptr(self.nodes), _ptr(loc), _ptr(gids), int(ord_base), f, self.m, int(self.cyc), G,
+                                              self.rcap, _ptr(counts), dst, self.stream), "acx_pbfs_expand")
+        return counts
+
+    def probe(self, n_parents):
+        rc, nreg, rcap = self._region_args()
+        self._slot = torch.empty((nreg * rcap,), dtype=torch.int64, device=self.dev)
+        mask = torch.zeros((n_parents,), dtype=torch.int32, device=self.dev)
+        mins = torch.full((2,), -1, dtype=torch.int64, device=self.dev)
+        if sum(self._regions):
+            _lib.check(self.L.acx_pbfs_probe(_ptr(self._recv), rc, nreg, rcap, _ptr(self.table), self.tcap, _ptr(self.nodes),
+                                             _ptr(self._slot), _ptr(mins), _ptr(mask), self.stream), "acx_pbfs_probe")
+        mins = torch.where(mins < 0, torch.full_like(mins, SENT), mins)
+        return mask, mins
+
+    def commit(self, excl_par, gmask, parent_base, gid_base):
+        rc, nreg, rcap = self._region_args()
+        if sum(self._regions):
+            _lib.check(self.L.acx_pbfs_commit(_ptr(self._recv), rc, nreg, rcap, _ptr(self._slot), _ptr(excl_par), _ptr(gmask),
+                                              parent_base, gid_base, _ptr(self.n_local_dev), _ptr(self.table), _ptr(self.nodes),
+                                              _ptr(self.gid), _ptr(self.parent), _ptr(self.action), self.stream), "acx_pbfs_commit")
+
+
+def make_shard(root, cyclical, cap_local, max_parents, device, transport="auto"):
+    """PlaneShard when the root is inside the plane domain (every Miller-Schupp / AK(n) presentation), else GpuShard"""
+    root = np.ascontiguousarray(np.asarray(root), dtype=np.int8)
+    m = len(root) // 2
+    if m <= 36:
+        sh = PlaneShard(m, cyclical, cap_local, max_parents, device, transport)
+        if sh.accepts(root):
+            return sh
+        del sh
+    return GpuShard(m, cyclical, cap_local, max_parents, device, "nccl" if (transport == "auto" and m != 36) else transport)
+
+
 class ShardedBFS:
     def __init__(self, root, budget, shard, chunk=1 << 20, group=None):
         self.root = np.ascontiguousarray(np.asarray(root), dtype=np.int8)
@@ -302,7 +420,7 @@ class ShardedBFS:
         rec = torch.zeros((3,), dtype=torch.int64, device=self.dev)
         if hit.numel():
             k = hit[0]
-            rec = torch.stack([s.parent[k] + 1, s.action[k].to(torch.int64), s.total[k].to(torch.int64)])
+            rec = torch.stack([s.parent[k] + 1, s.action[k].to(torch.int64), s.node_total(k)])
         dist.all_reduce(rec, group=self.group)
         return int(rec[0]) - 1, int(rec[1]), int(rec[2])
 
@@ -325,11 +443,16 @@ class ShardedBFS:
             self.levels.append(hi - lo)
             self._tick(None)
             n_local = s.n_local()
-            gids, perm = torch.sort(s.gid[first:n_local])  # local frontier in global discovery order
+            # group the local frontier by round (window of `chunk` consecutive global ids); inside a window the
+            # order is free, so a narrow-key sort on the window index is enough (2-4 radix passes, not 8)
+            gl = s.gid[first:n_local]
+            nwin = (hi - lo + self.chunk - 1) // self.chunk
+            widx = (gl - lo) // self.chunk
+            widx, perm = torch.sort(widx.to(torch.int16 if nwin < 32768 else torch.int32))
             loc = perm + first
+            gids = gl[perm]
             first = n_local
-            bounds = torch.arange(lo, hi + self.chunk, self.chunk, device=dev).clamp_(max=hi)
-            cuts = torch.searchsorted(gids, bounds).tolist()
+            cuts = torch.searchsorted(widx, torch.arange(nwin + 1, device=dev, dtype=widx.dtype)).tolist()
             self._tick("level_sort")
             for k, off in enumerate(range(lo, hi, self.chunk)):
                 C = min(self.chunk, hi - off)

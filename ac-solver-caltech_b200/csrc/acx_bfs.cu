@@ -492,6 +492,8 @@ __global__ void __launch_bounds__(32 * WARPS) k_bfs_expand_bucket(const int8_t* 
                         if (changed) {
                             if (cyc) Ops::cyclic(x);
                             Ops::unpack(child + (d & 1u) * MS, x);
+                            const R& old = i ? rc[1] : rc[0];
+                            moved = !(x.n == old.n && x.S == old.S && x.T == old.T);
                         }
                         const int na = changed ? x.n : (i ? rc[1].n : rc[0].n);
                         l0 = i ? rc[0].n : na;

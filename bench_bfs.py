@@ -39,7 +39,7 @@ def run_sharded(budget=10 ** 8, chunk_per_rank=1 << 20):
     A round expands `chunk_per_rank` parents per rank (the result does not depend on the chunk)."""
     import torch.distributed as dist
 
-    from acx.bfs_sharded import GpuShard, ShardedBFS
+    from acx.bfs_sharded import GpuShard, ShardedBFS, make_shard
 
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -51,7 +51,11 @@ def run_sharded(budget=10 ** 8, chunk_per_rank=1 << 20):
     for b in (10 ** 6, budget):  # first pass = warm-up (NCCL channels, kernels)
         cap_local = int(b / world * (1.0 if world == 1 else 1.06)) + 4096
         max_parents = chunk if world == 1 else min(chunk, int(chunk / world * 1.15) + 8192)
-        shard = GpuShard(36, False, cap_local, max_parents, str(dev), transport=os.environ.get("ACX_BFS_TRANSPORT", "auto"))
+        transport = os.environ.get("ACX_BFS_TRANSPORT", "auto")
+        if os.environ.get("ACX_BFS_NODES", "planes") == "bytes":
+            shard = GpuShard(36, False, cap_local, max_parents, str(dev), transport=transport)
+        else:
+            shard = make_shard(ak3(), False, cap_local, max_parents, str(dev), transport=transport)
         eng = ShardedBFS(ak3(), b, shard, chunk=chunk)
         if os.environ.get("ACX_BFS_PROF"):
             eng.timers = {}
@@ -67,7 +71,7 @@ def run_sharded(budget=10 ** 8, chunk_per_rank=1 << 20):
         out = {"config": "configs[3] hash-partitioned level-synchronous bfs from AK(3), m=36, budget %d" % b,
                "n_gpus": world, "solved": ok, "n_seen": eng.n_nodes, "nodes_expanded": eng.n_expanded, "wall_s": float(dt[0]),
                "nodes_expanded_per_s": eng.n_expanded / float(dt[0]), "all_to_all_bytes_total": int(sent[0]),
-               "scaling": "strong", "chunk_parents_per_round": chunk, "transport": shard.transport, "levels": eng.levels}
+               "scaling": "strong", "chunk_parents_per_round": chunk, "transport": shard.transport, "nodes": type(shard).__name__, "levels": eng.levels}
         if eng.timers is not None:
             out["phase_s_rank0"] = {k: round(v, 5) for k, v in eng.timers.items()}
         shard.close()

@@ -176,6 +176,30 @@ int acx_bfs_commit_packed(const uint8_t* recs, const int64_t* region_counts, int
                           int64_t gid_base, uint64_t* n_local, uint64_t* table, int8_t* nodes, int64_t* gid, int64_t* parent,
                           uint8_t* action, uint16_t* total, acx_stream_t stream);
 
+/* Bit-plane bfs (max_relator_length <= 36, presentations over {x, y} with a freely reduced root -- cyclically
+ * reduced too when cyclical): a node is four 64-bit words
+ *     w0 = S(r0) | len(r0) << 40    w1 = T(r0) | len(r1) << 40    w2 = S(r1)    w3 = T(r1)
+ * (S: letter is an inverse, T: letter is y; bit k = letter k), 32 bytes instead of 2m; a candidate record is the
+ * same 32 bytes with its order (48 bits) and row status (2 bits) in the spare top bits of w2 / w3.  Same search
+ * semantics and the same region / order / mask protocol as acx_bfs_expand_bucket, acx_bfs_probe_packed and
+ * acx_bfs_commit_packed (breadth_first.py:52-95); `total` of a node is len(r0) + len(r1).
+ *   acx_pbfs_pack    byte rows -> nodes; ok_out[j] = 0 when row j is outside the plane domain (use the byte kernels)
+ *   acx_pbfs_unpack  nodes -> byte rows */
+int acx_pbfs_pack(const int8_t* rows, int64_t n, int m, int cyclical, uint64_t* nodes_out, uint8_t* ok_out,
+                  acx_stream_t stream);
+int acx_pbfs_unpack(const uint64_t* nodes, int64_t n, int m, int8_t* rows_out, acx_stream_t stream);
+int acx_pbfs_hash(const uint64_t* nodes, int64_t n, uint64_t* hash_out, acx_stream_t stream);
+int acx_pbfs_seed(const uint64_t* node, uint64_t* table, int64_t tcap, int64_t node_id, acx_stream_t stream);
+int acx_pbfs_expand(const uint64_t* nodes, const int64_t* loc, const int64_t* gids, int64_t ord_base, int64_t f, int m,
+                    int cyclical, int world, int64_t region_cap, uint64_t* cursor, uint8_t* const* dst_regions,
+                    acx_stream_t stream);
+int acx_pbfs_probe(const uint64_t* recs, const int64_t* region_counts, int n_regions, int64_t region_cap, uint64_t* table,
+                   int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins, int32_t* mask, acx_stream_t stream);
+int acx_pbfs_commit(const uint64_t* recs, const int64_t* region_counts, int n_regions, int64_t region_cap,
+                    const int64_t* slot, const int64_t* excl_par, const int32_t* gmask, int64_t parent_base,
+                    int64_t gid_base, uint64_t* n_local, uint64_t* table, uint64_t* nodes, int64_t* gid, int64_t* parent,
+                    uint8_t* action, acx_stream_t stream);
+
 /* Peer memory (CUDA IPC): a receive buffer the other ranks of one NVLink domain write into directly, so that
  * acx_bfs_expand_bucket IS the all-to-all (stores over NVLink from inside the kernel, no staging, no collective). */
 int acx_peer_alloc(int64_t bytes, void** ptr);

@@ -59,7 +59,7 @@ def test_sharded_bfs_single_rank_gpu(cuda, oracle, golden_dir):
     import torch
     import torch.distributed as dist
 
-    from acx.bfs_sharded import GpuShard, ShardedBFS
+    from acx.bfs_sharded import GpuShard, PlaneShard, ShardedBFS
 
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", str(29700 + os.getpid() % 200))
@@ -73,13 +73,67 @@ def test_sharded_bfs_single_rank_gpu(cuda, oracle, golden_dir):
             for budget, chunk in ((1, 4), (14, 4), (700, 64), (30000, 4096)):
                 cyc = bool(rng.integers(0, 2))
                 row = rows[int(k)]
-                shard = GpuShard(len(row) // 2, cyc, budget + 64, chunk, str(cuda))
-                eng = ShardedBFS(row, budget, shard, chunk=chunk)
-                ok, path = eng.run()
                 stats = {}
                 ook, opath = oracle.bfs(row, budget, False, cyc, stats=stats)
-                assert (ok, path) == (ook, opath), (int(k), budget, cyc)
-                assert eng.n_nodes == stats["n_seen"] and eng.n_expanded == stats["n_expanded"]
+                for kind in (GpuShard, PlaneShard):
+                    shard = kind(len(row) // 2, cyc, budget + 64, chunk, str(cuda))
+                    if kind is PlaneShard and not shard.accepts(row):
+                        continue
+                    eng = ShardedBFS(row, budget, shard, chunk=chunk)
+                    ok, path = eng.run()
+                    assert (ok, path) == (ook, opath), (int(k), budget, cyc, kind.__name__)
+                    assert eng.n_nodes == stats["n_seen"] and eng.n_expanded == stats["n_expanded"], kind.__name__
     finally:
         if created:
             dist.destroy_process_group()
+
+
+def test_plane_nodes_pack_expand_unpack(cuda, oracle, golden_dir):
+    """plane nodes: pack / unpack round trip, and acx_pbfs_expand == the oracle's 12 ACMoves (children equal to
+    their parent are dropped, everything else arrives with the right order number, lengths and letters)"""
+    import ctypes
+
+    import torch
+
+    from acx import _lib
+    from acx.batch import _ptr
+    from acx.bfs_sharded import PlaneShard
+    from helpers import random_rows
+
+    rng = np.random.default_rng(77)
+    for m, cyc in ((36, False), (36, True), (18, True), (7, False), (25, True)):
+        rows = random_rows(rng, 3000, m, kinds=(0, 1, 2, 3, 3, 2))
+        sh = PlaneShard(m, cyc, 16, 16, str(cuda))
+        nodes, ok = sh.pack(rows)
+        ok = ok.cpu().numpy().astype(bool)
+        assert ok.sum() > 100
+        back = sh.unpack(nodes).cpu().numpy()
+        assert (back[ok] == rows[ok]).all()
+        good = nodes[torch.from_numpy(ok).to(cuda)].contiguous()
+        rows_ok = rows[ok]
+        f = good.shape[0]
+        loc = torch.arange(f, device=cuda)
+        gids = torch.arange(f, device=cuda) + 1000
+        cursor = torch.zeros((2,), dtype=torch.int64, device=cuda)
+        out = torch.zeros((12 * f, 4), dtype=torch.int64, device=cuda)
+        dst = (ctypes.c_void_p * 1)(out.data_ptr())
+        _lib.check(sh.L.acx_pbfs_expand(_ptr(good), _ptr(loc), _ptr(gids), 1000, f, m, int(cyc), 1, 12 * f, _ptr(cursor), dst,
+                                        sh.stream), "acx_pbfs_expand")
+        n = int(cursor[0])
+        assert int(cursor[1]) == 0
+        rec = out[:n]
+        order = (((rec[:, 2] >> 36) & 0xFFFFFFF) | (((rec[:, 3] >> 36) & 0xFFFFF) << 28)).cpu().numpy()
+        status = ((rec[:, 3] >> 56) & 3).cpu().numpy()
+        state = rec.clone()
+        state[:, 2] &= (1 << 36) - 1
+        state[:, 3] &= (1 << 36) - 1
+        got_rows = sh.unpack(state).cpu().numpy()
+        ch, ln, st = oracle.expand12_batch(rows_ok, cyclical=cyc)
+        ch, st = ch.reshape(f * 12, 2 * m), st.reshape(f * 12)
+        assert len(set(order.tolist())) == n
+        seen = np.zeros(f * 12, dtype=bool)
+        seen[order] = True
+        assert (got_rows == ch[order]).all()
+        assert (status == st[order]).all()
+        same = (ch == np.repeat(rows_ok, 12, axis=0)).all(axis=1) & (st == 0)
+        assert (seen == ~same).all()  # exactly the children that differ from their parent (or raise) are sent

@@ -21,13 +21,16 @@ def _worker(rank, world, port, cases, out):
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    from acx.bfs_sharded import GpuShard, ShardedBFS
+    from acx.bfs_sharded import GpuShard, PlaneShard, ShardedBFS
 
     res = []
     for row, budget, cyc, chunk in cases:
         row = np.array(row, dtype=np.int8)
-        for transport in ("auto", "nccl"):  # auto = peer stores over NVLink for m = 36
-            shard = GpuShard(len(row) // 2, cyc, budget + 64, chunk, str(dev), transport=transport)
+        for kind, transport in ((GpuShard, "auto"), (GpuShard, "nccl"), (PlaneShard, "auto"), (PlaneShard, "nccl")):
+            shard = kind(len(row) // 2, cyc, budget + 64, chunk, str(dev), transport=transport)  # auto = peer stores over NVLink
+            if kind is PlaneShard and not shard.accepts(row):
+                res.append(None)
+                continue
             eng = ShardedBFS(row, budget, shard, chunk=chunk)
             ok, path = eng.run()
             shard.close()
@@ -75,8 +78,11 @@ def test_sharded_bfs_two_gpus_matches_oracle(cuda, oracle, golden_dir):
         stats = {}
         ok, path = oracle.bfs(np.array(row, dtype=np.int8), budget, False, cyc, stats=stats)
         for rank in (0, 1):
-            for t in (0, 1):
-                rok, rpath, n_seen, n_exp, transport = got[rank][2 * idx + t]
-                assert (rok, rpath) == (ok, path), (idx, rank, transport)
-                assert n_seen == stats["n_seen"] and n_exp == stats["n_expanded"], (idx, rank, transport)
-        assert got[0][2 * idx][4] == ("p2p" if len(row) == 72 else "nccl")
+            for t in range(4):
+                if got[rank][4 * idx + t] is None:
+                    continue
+                rok, rpath, n_seen, n_exp, transport = got[rank][4 * idx + t]
+                assert (rok, rpath) == (ok, path), (idx, rank, t, transport)
+                assert n_seen == stats["n_seen"] and n_exp == stats["n_expanded"], (idx, rank, t, transport)
+        assert got[0][4 * idx][4] == ("p2p" if len(row) == 72 else "nccl")
+        assert got[0][4 * idx + 2] is None or got[0][4 * idx + 2][4] == "p2p"
