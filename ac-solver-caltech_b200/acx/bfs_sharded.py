@@ -137,9 +137,12 @@ class GpuShard:
                 # my region inside every owner's receive buffer
                 self.dst.append([bases[g] + rank * self.rcap * self.rec for g in range(G)])
         elif self.fused:
-            self.send = torch.empty((G * self.rcap, self.rec), dtype=torch.uint8, device=self.dev)
-            self.dst = [[self.send.data_ptr() + g * self.rcap * self.rec for g in range(G)]] * 2
+            # two send buffers: round k + 1 may be staged while round k is still being exchanged / probed
+            self.sends = [torch.empty((G * self.rcap, self.rec), dtype=torch.uint8, device=self.dev) for _ in range(2)]
+            self.dst = [[b.data_ptr() + g * self.rcap * self.rec for g in range(G)] for b in self.sends]
         self._group = group
+        # frontier index buffers of a level (local index, global id), allocated once: a level can be most of the shard
+        self._part = (torch.empty((self.cap,), dtype=torch.int64, device=self.dev), torch.empty((self.cap,), dtype=torch.int64, device=self.dev))
 
     def _fusable(self, world):
         return self.m == 36 and world <= 32
@@ -227,13 +230,44 @@ class GpuShard:
             send = self._packed if self._packed is not None else torch.empty((0, self.rec), dtype=torch.uint8, device=self.dev)
             starts = [sum(scl[:g]) for g in range(G)]
         else:
-            send, starts = self.send, [g * self.rcap for g in range(G)]
+            send, starts = self.sends[k % 2], [g * self.rcap for g in range(G)]
         if G == 1:
             self._recv, self._regions, self._rcap_now = send[starts[0]:starts[0] + scl[0]], [scl[0]], max(scl[0], 1)
             return
         recv = torch.empty((sum(rcl), self.rec), dtype=torch.uint8, device=self.dev)
         dist.all_to_all(list(recv.split(rcl)), [send[starts[g]:starts[g] + scl[g]] for g in range(G)], group=self._group)
         self._recv, self._regions, self._rcap_now = recv, [sum(rcl)], max(sum(rcl), 1)
+
+    def window_partition(self, gl, first, lo, chunk, nwin):
+        """local frontier (global ids gl, stored from local index `first`) grouped by round: (loc, gids, cuts)"""
+        n = gl.shape[0]
+        d = self.dev
+        counts = torch.zeros((nwin,), dtype=torch.int64, device=d)
+        loc, gids = self._part[0][:n], self._part[1][:n]
+        if n:
+            gl = gl.contiguous()
+            _lib.check(self.L.acx_bfs_window_partition(_ptr(gl), n, lo, chunk, nwin, _ptr(counts), 0, 0, first, 0, 0, 0, self.stream),
+                       "acx_bfs_window_partition")
+        ends = torch.cumsum(counts, 0)
+        if n:
+            offsets = (ends - counts).contiguous()
+            cursor = torch.zeros((nwin,), dtype=torch.int64, device=d)
+            _lib.check(self.L.acx_bfs_window_partition(_ptr(gl), n, lo, chunk, nwin, _ptr(counts), _ptr(offsets), _ptr(cursor), first,
+                                                       _ptr(loc), _ptr(gids), 1, self.stream), "acx_bfs_window_partition")
+        return loc, gids, [0] + ends.tolist()
+
+    def mask_scan(self, mask):
+        """(exclusive scan of popcount(mask), total) on the device, one cub pass"""
+        n = mask.shape[0]
+        excl = torch.empty((n,), dtype=torch.int64, device=self.dev)
+        total = torch.zeros((1,), dtype=torch.int64, device=self.dev)
+        need = int(self.L.acx_bfs_mask_scan(0, n, 0, 0, 0, 0, self.stream))
+        if need < 0:
+            _lib.check(need, "acx_bfs_mask_scan")
+        temp = torch.empty((max(need, 1),), dtype=torch.uint8, device=self.dev)
+        _lib.check(int(self.L.acx_bfs_mask_scan(_ptr(mask), n, _ptr(excl), _ptr(total), _ptr(temp), need, self.stream)),
+                   "acx_bfs_mask_scan")
+        return excl, total
 
     def _region_args(self):
         import ctypes
@@ -327,7 +361,9 @@ class PlaneShard(GpuShard):
         w = self.nodes[k]
         return ((w[0] >> 40) & 63) + ((w[1] >> 40) & 63)
 
-    def stage(self, loc, gids, ord_base, k):
+    overlap = True  # stage(k + 1) may run on a side stream while round k is probed and committed
+
+    def stage(self, loc, gids, ord_base, k, stream=None, ctas=0):
         import ctypes
 
         G, f = self.world, loc.shape[0]
@@ -339,7 +375,8 @@ class PlaneShard(GpuShard):
             loc, gids = loc.contiguous(), gids.contiguous()
             dst = (ctypes.c_void_p * G)(*self.dst[k % 2])
             _lib.check(self.L.acx_pbfs_expand(_ptr(self.nodes), _ptr(loc), _ptr(gids), int(ord_base), f, self.m, int(self.cyc), G,
-                                              self.rcap, _ptr(counts), dst, self.stream), "acx_pbfs_expand")
+                                              self.rcap, _ptr(counts), dst, ctas, self.stream if stream is None else stream),
+                       "acx_pbfs_expand")
         return counts
 
     def probe(self, n_parents):
@@ -374,7 +411,7 @@ def make_shard(root, cyclical, cap_local, max_parents, device, transport="auto")
 
 
 class ShardedBFS:
-    def __init__(self, root, budget, shard, chunk=1 << 20, group=None):
+    def __init__(self, root, budget, shard, chunk=1 << 20, group=None, pipeline=True, stage_ctas=2):
         self.root = np.ascontiguousarray(np.asarray(root), dtype=np.int8)
         self.budget = max(1, int(budget))
         self.shard = shard
@@ -384,6 +421,7 @@ class ShardedBFS:
         self.dev = shard.dev
         self.n_nodes, self.n_expanded, self.levels = 1, 0, []
         self.comm_bytes, self.rounds = 0, 0
+        self.pipeline, self.stage_ctas = bool(pipeline), int(stage_ctas)
         shard.connect(group)
         self.timers = None  # set to {} to collect a per-phase wall-clock breakdown (adds a device sync per phase)
         self._t0 = 0.0
@@ -397,6 +435,11 @@ class ShardedBFS:
         if name is not None:
             self.timers[name] = self.timers.get(name, 0.0) + now - self._t0
         self._t0 = now
+
+    def _drain(self):
+        side, main = self._side
+        if side is not None:
+            main.wait_stream(side)  # a staged round may still be in flight
 
     def _exchange(self, counts, k):
         """every rank learns how many records each rank staged for each owner (this all-gather is also the barrier
@@ -437,6 +480,10 @@ class ShardedBFS:
         s, G, dev = self.shard, self.world, self.dev
         if s.owner_of_row(self.root, G) == self.rank:
             s.seed(self.root)
+        side = main = None
+        if self.pipeline and G > 1 and getattr(s, "overlap", False) and dev.type == "cuda":
+            side, main = torch.cuda.Stream(dev), torch.cuda.current_stream(dev)
+        self._side = (side, main)
         lo, hi = 0, 1
         first = 0  # local index of the first node this rank discovered in the current frontier level
         while lo < hi:
@@ -447,29 +494,57 @@ class ShardedBFS:
             # order is free, so a narrow-key sort on the window index is enough (2-4 radix passes, not 8)
             gl = s.gid[first:n_local]
             nwin = (hi - lo + self.chunk - 1) // self.chunk
-            widx = (gl - lo) // self.chunk
-            widx, perm = torch.sort(widx.to(torch.int16 if nwin < 32768 else torch.int32))
-            loc = perm + first
-            gids = gl[perm]
+            if hasattr(s, "window_partition"):
+                loc, gids, cuts = s.window_partition(gl, first, lo, self.chunk, nwin)
+            else:
+                widx = (gl - lo) // self.chunk
+                widx, perm = torch.sort(widx.to(torch.int16 if nwin < 32768 else torch.int32))
+                loc = perm + first
+                gids = gl[perm]
+                cuts = torch.searchsorted(widx, torch.arange(nwin + 1, device=dev, dtype=widx.dtype)).tolist()
             first = n_local
-            cuts = torch.searchsorted(widx, torch.arange(nwin + 1, device=dev, dtype=widx.dtype)).tolist()
             self._tick("level_sort")
-            for k, off in enumerate(range(lo, hi, self.chunk)):
-                C = min(self.chunk, hi - off)
-                a, b = cuts[k], cuts[k + 1]
-                counts = s.stage(loc[a:b], gids[a:b], off, self.rounds)
+            rounds = [(off, min(self.chunk, hi - off), cuts[k], cuts[k + 1]) for k, off in enumerate(range(lo, hi, self.chunk))]
+            k0 = self.rounds
+            if side is not None:
+                side.wait_stream(main)  # loc / gids of this level are ready
+
+            def launch(i):
+                off, C, a, b = rounds[i]
+                if side is None:
+                    return s.stage(loc[a:b], gids[a:b], off, k0 + i), None
+                with torch.cuda.stream(side):
+                    c = s.stage(loc[a:b], gids[a:b], off, k0 + i, stream=side.cuda_stream, ctas=self.stage_ctas)
+                    c.record_stream(main)
+                    return c, side.record_event()
+
+            pending = launch(0)
+            for i, (off, C, a, b) in enumerate(rounds):
+                counts, ev = pending
+                if ev is not None:
+                    main.wait_event(ev)
                 self._tick("expand_bucket")
-                self.comm_bytes += self._exchange(counts, self.rounds)
+                self.comm_bytes += self._exchange(counts, k0 + i)
                 self.rounds += 1
+                # every rank has now finished round i - 1 (its all-gather contribution comes after its commit), so
+                # the buffers of round i + 1 are free: stage it next to the probe / commit of round i
+                pending = launch(i + 1) if i + 1 < len(rounds) else None
                 self._tick("all_to_all")
                 mask, mins = s.probe(C)
                 self._tick("probe")
                 if G > 1:
+                    if self.timers is not None:
+                        dist.barrier(group=self.group)
+                        self._tick("wait_slowest_rank")
                     dist.all_reduce(mask, group=self.group)
                     dist.all_reduce(mins, op=dist.ReduceOp.MIN, group=self.group)
-                cnt = popcount_lut(mask)
-                cum = torch.cumsum(cnt, dim=0)
-                c_s, c_e, n_new = torch.cat([mins, cum[-1:]]).tolist()
+                if hasattr(s, "mask_scan"):
+                    excl, total = s.mask_scan(mask)
+                else:
+                    cnt = popcount_lut(mask)
+                    excl = torch.cumsum(cnt, dim=0) - cnt
+                    total = excl[-1:] + cnt[-1:]
+                c_s, c_e, n_new = torch.cat([mins, total]).tolist()
                 self._tick("reduce_scan")
                 events = []
                 if c_s < SENT:
@@ -478,23 +553,28 @@ class ShardedBFS:
                     events.append((c_e, 0, "error"))
                 p_star = None
                 if self.n_nodes + n_new >= self.budget:
-                    # first parent after which len(tree_nodes) >= max_nodes_to_explore (breadth_first.py:91-95)
-                    p_star = int(torch.searchsorted(cum, torch.tensor([self.budget - self.n_nodes], device=dev))[0])
+                    # first parent after which len(tree_nodes) >= max_nodes_to_explore (breadth_first.py:91-95):
+                    # inclusive count of parent p = excl[p + 1] (or the round total for the last parent)
+                    idx = int(torch.searchsorted(excl, torch.tensor([self.budget - self.n_nodes], device=dev))[0])
+                    p_star = max(idx - 1, 0)
                     events.append((12 * p_star + 11, 1, "budget"))
                 if events:
                     pos, _, what = min(events)
                     if what == "solved":
                         self.n_expanded += pos // 12 + 1
                         p, aa = pos // 12, pos % 12
-                        before = int(cum[p] - cnt[p]) + int(popcount12(mask[p].to(torch.int64) & ((1 << aa) - 1)))
+                        before = int(excl[p]) + int(popcount12(mask[p].to(torch.int64) & ((1 << aa) - 1)))
                         self.n_nodes += before
+                        self._drain()
                         return True, self._path(off + p, aa)
                     if what == "error":
+                        self._drain()
                         raise AssertionError("a relator became empty during the search: not a valid presentation")
                     self.n_expanded += p_star + 1
-                    self.n_nodes += int(cum[p_star])
+                    self.n_nodes += int(excl[p_star]) + int(popcount12(mask[p_star].to(torch.int64)))
+                    self._drain()
                     return False, None
-                s.commit(cum - cnt, mask, off, self.n_nodes)
+                s.commit(excl, mask, off, self.n_nodes)
                 self._tick("commit")
                 self.n_nodes += n_new
                 self.n_expanded += C

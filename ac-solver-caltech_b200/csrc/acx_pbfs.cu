@@ -21,6 +21,9 @@
 #include "acx_common.h"
 #include "acx_rows.cuh"
 
+#include <cub/device/device_scan.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
+
 namespace acx {
 
 static constexpr int PB_MAX_WORLD = 32;
@@ -34,19 +37,15 @@ struct PWords {
     uint64_t w[4];
 };
 
+// one 256-bit access per node / record (LDG.256 / STG.256 on sm_100): a whole 32-byte sector per lane
 __device__ __forceinline__ PWords pb_load(const uint64_t* p) {
-    const uint4 a = reinterpret_cast<const uint4*>(p)[0], b = reinterpret_cast<const uint4*>(p)[1];
     PWords o;
-    o.w[0] = (uint64_t)a.x | ((uint64_t)a.y << 32);
-    o.w[1] = (uint64_t)a.z | ((uint64_t)a.w << 32);
-    o.w[2] = (uint64_t)b.x | ((uint64_t)b.y << 32);
-    o.w[3] = (uint64_t)b.z | ((uint64_t)b.w << 32);
+    asm volatile("ld.global.v4.b64 {%0, %1, %2, %3}, [%4];" : "=l"(o.w[0]), "=l"(o.w[1]), "=l"(o.w[2]), "=l"(o.w[3]) : "l"(p) : "memory");
     return o;
 }
 
 __device__ __forceinline__ void pb_store(uint64_t* p, const PWords& v) {
-    reinterpret_cast<uint4*>(p)[0] = make_uint4((uint32_t)v.w[0], (uint32_t)(v.w[0] >> 32), (uint32_t)v.w[1], (uint32_t)(v.w[1] >> 32));
-    reinterpret_cast<uint4*>(p)[1] = make_uint4((uint32_t)v.w[2], (uint32_t)(v.w[2] >> 32), (uint32_t)v.w[3], (uint32_t)(v.w[3] >> 32));
+    asm volatile("st.global.v4.b64 [%0], {%1, %2, %3, %4};" ::"l"(p), "l"(v.w[0]), "l"(v.w[1]), "l"(v.w[2]), "l"(v.w[3]) : "memory");
 }
 
 __device__ __forceinline__ PWords pb_state(const PWords& v) {  // drop order / status
@@ -434,7 +433,7 @@ extern "C" int acx_pbfs_seed(const uint64_t* node, uint64_t* table, int64_t tcap
 
 extern "C" int acx_pbfs_expand(const uint64_t* nodes, const int64_t* loc, const int64_t* gids, int64_t ord_base, int64_t f, int m,
                                int cyclical, int world, int64_t region_cap, uint64_t* cursor, uint8_t* const* dst_regions,
-                               acx_stream_t stream) {
+                               int ctas_per_sm_limit, acx_stream_t stream) {
     if (f < 0 || m < 1 || m > PB_MAX_M || world < 1 || world > PB_MAX_WORLD || region_cap < 1)
         return acx_fail(ACX_ERR_ARG, "acx_pbfs_expand: bad argument (1 <= m <= 36, 1 <= world <= 32)");
     if (f == 0) return ACX_OK;
@@ -445,7 +444,7 @@ extern "C" int acx_pbfs_expand(const uint64_t* nodes, const int64_t* loc, const 
         if (!dst_regions[o] || ((uintptr_t)dst_regions[o] & 31u)) return acx_fail(ACX_ERR_ARG, "acx_pbfs_expand: destination regions must be non-null and 32-byte aligned");
         dst.region[o] = dst_regions[o];
     }
-    if ((uintptr_t)nodes & 15u) return acx_fail(ACX_ERR_ARG, "acx_pbfs_expand: nodes must be 16-byte aligned");
+    if ((uintptr_t)nodes & 31u) return acx_fail(ACX_ERR_ARG, "acx_pbfs_expand: nodes must be 32-byte aligned");
     static int ctas_per_sm[ACX_MAX_DEVICES] = {0};
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -459,7 +458,9 @@ extern "C" int acx_pbfs_expand(const uint64_t* nodes, const int64_t* loc, const 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int64_t ntiles = (f + 31) / 32;
     int64_t grid = (ntiles + 7) / 8;
-    if (grid > (int64_t)sms * ctas_per_sm[dev]) grid = (int64_t)sms * ctas_per_sm[dev];
+    int resident = ctas_per_sm[dev];
+    if (ctas_per_sm_limit > 0 && ctas_per_sm_limit < resident) resident = ctas_per_sm_limit;  // leave room for a concurrent kernel
+    if (grid > (int64_t)sms * resident) grid = (int64_t)sms * resident;
     kern<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(nodes, loc, gids, ord_base, f, m, cyclical, world, region_cap,
                                                           reinterpret_cast<unsigned long long*>(cursor), dst, ntiles);
     ACX_CUDA(cudaGetLastError());
@@ -495,6 +496,141 @@ extern "C" int acx_pbfs_commit(const uint64_t* recs, const int64_t* region_count
     p.parent_base = parent_base; p.gid_base = gid_base; p.n_local = reinterpret_cast<unsigned long long*>(n_local);
     p.nodes_w = nodes; p.gid = gid; p.parent = parent; p.action = action;
     k_pbfs_commit<<<(unsigned)((p.n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+namespace acx {
+struct PopcountMask {
+    __host__ __device__ __forceinline__ int64_t operator()(const int32_t& m) const {
+#ifdef __CUDA_ARCH__
+        return (int64_t)__popc((unsigned)m);
+#else
+        return (int64_t)__builtin_popcount((unsigned)m);
+#endif
+    }
+};
+__global__ void k_mask_total(const int32_t* mask, const int64_t* excl, int64_t n, int64_t* total) {
+    total[0] = excl[n - 1] + __popc((unsigned)mask[n - 1]);
+}
+}  // namespace acx
+
+// exclusive scan of popcount(mask[p]) over the parents of a round (one pass, cub): excl_out[p] = new nodes
+// discovered by parents before p, total_out[0] = new nodes of the round.  temp == null: return the scratch size.
+extern "C" int64_t acx_bfs_mask_scan(const int32_t* mask, int64_t n, int64_t* excl_out, int64_t* total_out, void* temp,
+                                     int64_t temp_bytes, acx_stream_t stream) {
+    if (n < 0 || n > 0x7FFFFFFFll) return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan: bad argument");
+    cub::TransformInputIterator<int64_t, PopcountMask, const int32_t*> in(mask, PopcountMask());
+    size_t need = 0;
+    cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, need, in, excl_out, (int)n, (cudaStream_t)stream);
+    if (e != cudaSuccess) return acx_fail(ACX_ERR_CUDA, "cub::DeviceScan (size query): %s", cudaGetErrorString(e));
+    if (!temp) return (int64_t)need;
+    if (n == 0) return ACX_OK;
+    if (!mask || !excl_out || !total_out) return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan: null pointer");
+    if ((size_t)temp_bytes < need) return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan: scratch too small");
+    size_t tb = (size_t)temp_bytes;
+    e = cub::DeviceScan::ExclusiveSum(temp, tb, in, excl_out, (int)n, (cudaStream_t)stream);
+    if (e != cudaSuccess) return acx_fail(ACX_ERR_CUDA, "cub::DeviceScan: %s", cudaGetErrorString(e));
+    k_mask_total<<<1, 1, 0, (cudaStream_t)stream>>>(mask, excl_out, n, total_out);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+namespace acx {
+// Group the local frontier of a level by round: window w = (gid - lo) / chunk.  Inside a window the order is free,
+// so a counting sort (histogram, scan on the host side, scatter) replaces a full sort.  Atomics are aggregated
+// per warp with match.any: consecutive local nodes were discovered in the same round and mostly share a window.
+// Block-level aggregation: a block handles WIN_ITEMS * 256 consecutive local nodes; they were discovered in one or two
+// rounds, so their windows span a short range [wmin, wmax] that is counted / ranked in shared memory, with one global
+// atomic per (block, window).  A block whose range exceeds the shared table falls back to per-element global atomics.
+static constexpr int WIN_ITEMS = 16, WIN_BINS = 1024;
+
+template <bool SCATTER>
+__global__ void __launch_bounds__(256) k_win_part(const int64_t* gid, int64_t n, int64_t lo, int64_t chunk, unsigned long long* counts,
+                                                  const int64_t* offsets, unsigned long long* cursor, int64_t first,
+                                                  int64_t* loc_out, int64_t* gid_out) {
+    __shared__ unsigned s_cnt[WIN_BINS];
+    __shared__ unsigned long long s_base[WIN_BINS];
+    __shared__ int s_wmin, s_wmax;
+    const int tid = threadIdx.x;
+    const int64_t i0 = (int64_t)blockIdx.x * (WIN_ITEMS * 256) + tid;
+    for (int t = tid; t < WIN_BINS; t += 256) s_cnt[t] = 0u;
+    if (tid == 0) {
+        s_wmin = 0x7FFFFFFF;
+        s_wmax = -1;
+    }
+    __syncthreads();
+    int64_t g[WIN_ITEMS];
+    int w[WIN_ITEMS];
+    int mn = 0x7FFFFFFF, mx = -1;
+#pragma unroll
+    for (int k = 0; k < WIN_ITEMS; ++k) {
+        const int64_t i = i0 + (int64_t)k * 256;
+        w[k] = -1;
+        g[k] = 0;
+        if (i < n) {
+            g[k] = gid[i];
+            w[k] = (int)((g[k] - lo) / chunk);
+            mn = min(mn, w[k]);
+            mx = max(mx, w[k]);
+        }
+    }
+    if (mx >= 0) {
+        atomicMin(&s_wmin, mn);
+        atomicMax(&s_wmax, mx);
+    }
+    __syncthreads();
+    const int wmin = s_wmin, range = s_wmax - s_wmin + 1;
+    if (range > WIN_BINS) {  // rare: straight global atomics
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; ++k) {
+            if (w[k] < 0) continue;
+            if (!SCATTER) {
+                atomicAdd(counts + w[k], 1ull);
+            } else {
+                const int64_t pos = offsets[w[k]] + (int64_t)atomicAdd(cursor + w[k], 1ull);
+                loc_out[pos] = first + i0 + (int64_t)k * 256;
+                gid_out[pos] = g[k];
+            }
+        }
+        return;
+    }
+    unsigned rank[WIN_ITEMS];
+#pragma unroll
+    for (int k = 0; k < WIN_ITEMS; ++k) rank[k] = w[k] >= 0 ? atomicAdd(&s_cnt[w[k] - wmin], 1u) : 0u;
+    __syncthreads();
+    for (int t = tid; t < range; t += 256) {
+        if (!s_cnt[t]) continue;
+        if (!SCATTER) atomicAdd(counts + wmin + t, (unsigned long long)s_cnt[t]);
+        else s_base[t] = atomicAdd(cursor + wmin + t, (unsigned long long)s_cnt[t]);
+    }
+    if (!SCATTER) return;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < WIN_ITEMS; ++k) {
+        if (w[k] < 0) continue;
+        const int64_t pos = offsets[w[k]] + (int64_t)s_base[w[k] - wmin] + rank[k];
+        loc_out[pos] = first + i0 + (int64_t)k * 256;
+        gid_out[pos] = g[k];
+    }
+}
+}  // namespace acx
+
+extern "C" int acx_bfs_window_partition(const int64_t* gid, int64_t n, int64_t lo, int64_t chunk, int64_t n_windows,
+                                        uint64_t* counts, const int64_t* offsets, uint64_t* cursor, int64_t first,
+                                        int64_t* loc_out, int64_t* gid_out, int phase, acx_stream_t stream) {
+    if (n < 0 || chunk < 1 || n_windows < 1 || n_windows > 0x7FFFFFFF) return acx_fail(ACX_ERR_ARG, "acx_bfs_window_partition: bad argument");
+    if (n == 0) return ACX_OK;
+    const unsigned grid = (unsigned)((n + WIN_ITEMS * 256 - 1) / (WIN_ITEMS * 256));
+    if (phase == 0) {
+        if (!gid || !counts) return acx_fail(ACX_ERR_ARG, "acx_bfs_window_partition: null pointer");
+        k_win_part<false><<<grid, 256, 0, (cudaStream_t)stream>>>(gid, n, lo, chunk, reinterpret_cast<unsigned long long*>(counts), nullptr,
+                                                                 nullptr, first, nullptr, nullptr);
+    } else {
+        if (!gid || !offsets || !cursor || !loc_out || !gid_out) return acx_fail(ACX_ERR_ARG, "acx_bfs_window_partition: null pointer");
+        k_win_part<true><<<grid, 256, 0, (cudaStream_t)stream>>>(gid, n, lo, chunk, nullptr, offsets,
+                                                                reinterpret_cast<unsigned long long*>(cursor), first, loc_out, gid_out);
+    }
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }

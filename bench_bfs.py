@@ -48,6 +48,12 @@ def run_sharded(budget=10 ** 8, chunk_per_rank=1 << 20):
     dist.init_process_group("nccl", device_id=dev)
     out = None
     chunk = chunk_per_rank * world
+    if world > 1:  # NCCL connects lazily per algorithm / message size: touch the sizes the search uses
+        for _ in range(3):
+            dist.all_reduce(torch.zeros(chunk, dtype=torch.int32, device=dev))
+            dist.all_reduce(torch.zeros(2, dtype=torch.int64, device=dev), op=dist.ReduceOp.MIN)
+            dist.all_gather_into_tensor(torch.zeros(world * (world + 1), dtype=torch.int64, device=dev),
+                                        torch.zeros(world + 1, dtype=torch.int64, device=dev))
     for b in (10 ** 6, budget):  # first pass = warm-up (NCCL channels, kernels)
         cap_local = int(b / world * (1.0 if world == 1 else 1.06)) + 4096
         max_parents = chunk if world == 1 else min(chunk, int(chunk / world * 1.15) + 8192)
@@ -56,7 +62,8 @@ def run_sharded(budget=10 ** 8, chunk_per_rank=1 << 20):
             shard = GpuShard(36, False, cap_local, max_parents, str(dev), transport=transport)
         else:
             shard = make_shard(ak3(), False, cap_local, max_parents, str(dev), transport=transport)
-        eng = ShardedBFS(ak3(), b, shard, chunk=chunk)
+        eng = ShardedBFS(ak3(), b, shard, chunk=chunk, pipeline=os.environ.get("ACX_BFS_PIPELINE", "1") != "0",
+                         stage_ctas=int(os.environ.get("ACX_BFS_STAGE_CTAS", "2")))
         if os.environ.get("ACX_BFS_PROF"):
             eng.timers = {}
         dist.barrier()

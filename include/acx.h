@@ -192,6 +192,7 @@ int acx_pbfs_hash(const uint64_t* nodes, int64_t n, uint64_t* hash_out, acx_stre
 int acx_pbfs_seed(const uint64_t* node, uint64_t* table, int64_t tcap, int64_t node_id, acx_stream_t stream);
 int acx_pbfs_expand(const uint64_t* nodes, const int64_t* loc, const int64_t* gids, int64_t ord_base, int64_t f, int m,
                     int cyclical, int world, int64_t region_cap, uint64_t* cursor, uint8_t* const* dst_regions,
+                    int ctas_per_sm_limit /* 0 = fill the GPU; k = leave room for a kernel on another stream */,
                     acx_stream_t stream);
 int acx_pbfs_probe(const uint64_t* recs, const int64_t* region_counts, int n_regions, int64_t region_cap, uint64_t* table,
                    int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins, int32_t* mask, acx_stream_t stream);
@@ -199,6 +200,19 @@ int acx_pbfs_commit(const uint64_t* recs, const int64_t* region_counts, int n_re
                     const int64_t* slot, const int64_t* excl_par, const int32_t* gmask, int64_t parent_base,
                     int64_t gid_base, uint64_t* n_local, uint64_t* table, uint64_t* nodes, int64_t* gid, int64_t* parent,
                     uint8_t* action, acx_stream_t stream);
+
+/* Exclusive scan of popcount(mask[p]) over the parents of a round: excl_out[p] = new nodes discovered by the
+ * parents before p (reference order), total_out[0] = new nodes of the round.  temp == NULL returns the scratch
+ * size in bytes; otherwise 0 / a negative error. */
+int64_t acx_bfs_mask_scan(const int32_t* mask, int64_t n, int64_t* excl_out, int64_t* total_out, void* temp,
+                          int64_t temp_bytes, acx_stream_t stream);
+
+/* Group the local frontier of a level by round (window w = (gid - lo) / chunk of the global discovery ids; the
+ * order inside a window is free): phase 0 counts[w] += 1; phase 1 scatters loc_out / gid_out to
+ * offsets[w] + (running cursor[w]), offsets = exclusive scan of counts.  loc_out = first + index into gid. */
+int acx_bfs_window_partition(const int64_t* gid, int64_t n, int64_t lo, int64_t chunk, int64_t n_windows, uint64_t* counts,
+                             const int64_t* offsets, uint64_t* cursor, int64_t first, int64_t* loc_out, int64_t* gid_out,
+                             int phase, acx_stream_t stream);
 
 /* Peer memory (CUDA IPC): a receive buffer the other ranks of one NVLink domain write into directly, so that
  * acx_bfs_expand_bucket IS the all-to-all (stores over NVLink from inside the kernel, no staging, no collective). */

@@ -118,7 +118,7 @@ def test_plane_nodes_pack_expand_unpack(cuda, oracle, golden_dir):
         out = torch.zeros((12 * f, 4), dtype=torch.int64, device=cuda)
         dst = (ctypes.c_void_p * 1)(out.data_ptr())
         _lib.check(sh.L.acx_pbfs_expand(_ptr(good), _ptr(loc), _ptr(gids), 1000, f, m, int(cyc), 1, 12 * f, _ptr(cursor), dst,
-                                        sh.stream), "acx_pbfs_expand")
+                                        0, sh.stream), "acx_pbfs_expand")
         n = int(cursor[0])
         assert int(cursor[1]) == 0
         rec = out[:n]
