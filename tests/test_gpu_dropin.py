@@ -180,3 +180,21 @@ def test_vec_env_host_api(cuda, oracle, golden_dir):
         assert np.array_equal(env.lengths.cpu().numpy(), lens)
     env.envs[3].reset(options={"starting_state": pool[7]})
     assert np.array_equal(env.envs[3].state, pool[7]) and env.envs[3].count_steps == 0
+
+
+def test_bfs_large_budget_level_engine(cuda, oracle, golden_dir, capsys):
+    """budgets >= 2^16 go through the level-synchronous engine: same (solved, path), same exit message"""
+    from ac_solver.search import breadth_first
+    from helpers import AK3, dataset_rows, pad_row
+
+    rows = [r for r in dataset_rows(golden_dir) if len(r) == 72]
+    cases = [(pad_row(AK3[0], AK3[1], 36), 300000, False), (rows[700], 80000, True), (rows[3], 70000, False)]
+    for row, budget, cyc in cases:
+        assert budget >= breadth_first.LEVEL_SYNCHRONOUS_FROM
+        stats = {}
+        ook, opath = oracle.bfs(row, budget, False, cyc, stats=stats)
+        ok, path = breadth_first.bfs(row, budget, False, cyc)
+        assert (ok, path) == (ook, opath)
+        out = capsys.readouterr().out
+        if not ok and stats["n_seen"] >= budget:
+            assert f"explored nodes = {stats['n_seen']} has exceeded the limit {budget}" in out
