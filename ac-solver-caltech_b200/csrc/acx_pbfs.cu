@@ -370,12 +370,13 @@ __global__ void __launch_bounds__(256) k_pbfs_commit(const PbParams p) {
     const int act = (int)(ord % 12);
     const int64_t gid = p.gid_base + p.excl_par[par] + __popc((unsigned)p.gmask[par] & ((1u << act) - 1u));
     const int64_t id = (int64_t)atomicAdd(p.n_local, 1ull);
-    pb_store(p.nodes_w + 4 * id, pb_state(rec));
+    const PWords st = pb_state(rec);
+    pb_store(p.nodes_w + 4 * id, st);
     p.gid[id] = gid;
     p.parent[id] = p.parent_base + par;
     p.action[id] = (uint8_t)act;
-    const uint64_t e = p.table[s];
-    p.table[s] = (e & ~(PB_PROV | PB_VAL)) | (uint64_t)id;
+    // the slot keeps its tag (recomputed from the state: no read of the random table line) and now names the node
+    p.table[s] = (((pb_hash(st) >> 48) | 1ull) << 48) | (uint64_t)id;
 }
 
 static int pb_regions(PbParams& p, const int64_t* region_counts, int n_regions, int64_t region_cap, const char* who) {

@@ -31,6 +31,8 @@ M = 36
 N_ENV = 1 << 20
 HORIZON = 2000
 N_BATCHES = 4  # rotating resident batches: 4 x 75.5 MB of state > 126 MB L2
+# 89.28 MB read + 35.09 MB written per launch of 2^20 envs (ncu --set full capture, end of round 1)
+NCU_DRAM_BYTES_PER_LAUNCH = 124.4e6
 ALG_BYTES = 4 * M + 9  # read state 2m + action 1; write state 2m + lens 2 + reward 4 + done 1 + trunc 1
 METRIC = "AC-move transitions/sec (lockstep ACEnv.step)"
 UNIT = "transitions/s"
@@ -328,7 +330,11 @@ def gpu_arm(args):
                 "api": "acx.vecenv.VecACEnv.step(numpy actions) -> numpy obs/reward/done/truncated", "steps": e2e_steps},
         "gpu_launches": args.steps, "launch_mode": "python loop" if args.no_graph else "one CUDA graph of the K launches",
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "k_rows_tma<2,36,128,4,ENV>",
+                     "traffic": NCU_DRAM_BYTES_PER_LAUNCH if n == (1 << 20) else None,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full of this command "
+                                       "(profiles/r01_k_rows_tma_env_m36_ncu_full_summary.txt); below the algorithmic "
+                                       "bytes because the last stores of a 40 us kernel still sit in the 126 MB L2",
+                     "alg_bytes_per_launch": n * ALG_BYTES, "kernel": "k_rows_tma<W=2,MS=36,TR=128,S=3,ENV,CERT>",
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
                      "alg_bytes_per_transition": ALG_BYTES},
         "changed_row_fraction": changed,

@@ -188,7 +188,7 @@ def test_bfs_large_budget_level_engine(cuda, oracle, golden_dir, capsys):
     from helpers import AK3, dataset_rows, pad_row
 
     rows = [r for r in dataset_rows(golden_dir) if len(r) == 72]
-    cases = [(pad_row(AK3[0], AK3[1], 36), 300000, False), (rows[700], 80000, True), (rows[3], 70000, False)]
+    cases = [(pad_row(AK3[0], AK3[1], 36), 300000, False), (rows[len(rows) // 2], 80000, True), (rows[3], 70000, False)]
     for row, budget, cyc in cases:
         assert budget >= breadth_first.LEVEL_SYNCHRONOUS_FROM
         stats = {}
