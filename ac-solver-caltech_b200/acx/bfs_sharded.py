@@ -411,7 +411,7 @@ def make_shard(root, cyclical, cap_local, max_parents, device, transport="auto")
 
 
 class ShardedBFS:
-    def __init__(self, root, budget, shard, chunk=1 << 20, group=None, pipeline=True, stage_ctas=2):
+    def __init__(self, root, budget, shard, chunk=1 << 20, group=None, pipeline=False, stage_ctas=2):
         self.root = np.ascontiguousarray(np.asarray(root), dtype=np.int8)
         self.budget = max(1, int(budget))
         self.shard = shard
@@ -421,6 +421,8 @@ class ShardedBFS:
         self.dev = shard.dev
         self.n_nodes, self.n_expanded, self.levels = 1, 0, []
         self.comm_bytes, self.rounds = 0, 0
+        # pipeline=True stages round k + 1 on a side stream while round k is probed and committed.  Measured on 8 B200:
+        # no gain (the NVLink-bound staging kernel and the latency-bound probe slow each other down), so it is off.
         self.pipeline, self.stage_ctas = bool(pipeline), int(stage_ctas)
         shard.connect(group)
         self.timers = None  # set to {} to collect a per-phase wall-clock breakdown (adds a device sync per phase)
@@ -482,7 +484,8 @@ class ShardedBFS:
             s.seed(self.root)
         side = main = None
         if self.pipeline and G > 1 and getattr(s, "overlap", False) and dev.type == "cuda":
-            side, main = torch.cuda.Stream(dev), torch.cuda.current_stream(dev)
+            # high priority: the staging kernel is NVLink-bound and needs few SM slots, but it needs them early
+            side, main = torch.cuda.Stream(dev, priority=-1), torch.cuda.current_stream(dev)
         self._side = (side, main)
         lo, hi = 0, 1
         first = 0  # local index of the first node this rank discovered in the current frontier level

@@ -62,7 +62,7 @@ def run_sharded(budget=10 ** 8, chunk_per_rank=1 << 20):
             shard = GpuShard(36, False, cap_local, max_parents, str(dev), transport=transport)
         else:
             shard = make_shard(ak3(), False, cap_local, max_parents, str(dev), transport=transport)
-        eng = ShardedBFS(ak3(), b, shard, chunk=chunk, pipeline=os.environ.get("ACX_BFS_PIPELINE", "1") != "0",
+        eng = ShardedBFS(ak3(), b, shard, chunk=chunk, pipeline=os.environ.get("ACX_BFS_PIPELINE", "0") != "0",
                          stage_ctas=int(os.environ.get("ACX_BFS_STAGE_CTAS", "2")))
         if os.environ.get("ACX_BFS_PROF"):
             eng.timers = {}

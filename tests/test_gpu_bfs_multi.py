@@ -31,7 +31,7 @@ def _worker(rank, world, port, cases, out):
             if kind is PlaneShard and not shard.accepts(row):
                 res.append(None)
                 continue
-            eng = ShardedBFS(row, budget, shard, chunk=chunk)
+            eng = ShardedBFS(row, budget, shard, chunk=chunk, pipeline=(transport == "auto"))  # both schedules
             ok, path = eng.run()
             shard.close()
             res.append((ok, path, eng.n_nodes, eng.n_expanded, shard.transport))
