@@ -1,0 +1,100 @@
+// acx_replay.cu -- batched path replay: ACMove applied along a time axis.
+//
+// Replaces the Python loops that re-apply a list of actions to an initial presentation, one ACMove per
+// step: agents/training.py:74-135 (replay_final_state, actions_to_path), value_search/replay_path.py:107-160,
+// value_search/data_extraction.py:53-190.  One THREAD owns one path: the row stays in shared memory for the
+// whole path, every step is the same row function as the lockstep kernels (acmove_row64 / acmove_row), and
+// every intermediate state and length pair is emitted.  A step whose move empties a relator (the reference
+// raises AssertionError, utils.py:264-266), an invalid row or an action outside 0..11 stops that path:
+// status[p] names the reason, fail_step[p] the step.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/acx.h"
+#include "acx_common.h"
+#include "acx_rows.cuh"
+
+namespace acx {
+
+template <int W, int TR>
+__global__ void __launch_bounds__(TR) k_path_replay(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t P,
+                                                    int T, int m, int cyclical, int8_t* states_out, uint8_t* lens_out,
+                                                    int8_t* final_out, uint8_t* final_lens, int32_t* fail_step, uint8_t* status) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int rowb = 2 * m, pitch = (rowb + 7) / 8 * 8;
+    const int64_t p = (int64_t)blockIdx.x * TR + threadIdx.x;
+    if (p >= P) return;
+    uint8_t* row = smem + (size_t)threadIdx.x * pitch;
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(roots) + p * rowb;
+    int l0 = 0, l1 = 0;
+    for (int k = 0; k < rowb; ++k) {
+        const uint8_t v = src[k];
+        row[k] = v;
+        if (v) (k < m ? l0 : l1) += 1;
+    }
+    const int n = min(path_len ? path_len[p] : T, T);
+    uint32_t st = ACX_ROW_OK;
+    int fail = -1;
+    for (int t = 0; t < n; ++t) {
+        const int a = actions[p * T + t];
+        if (a >= 12) {
+            st = ACX_ROW_INVALID_INPUT;
+            fail = t;
+            break;
+        }
+        uint32_t s1 = ACX_ROW_OK;
+        if constexpr (W <= 2) acmove_row64<0>(row, m, a, cyclical != 0, l0, l1, s1);
+        else acmove_row<W, 0>(row, row, m, a, cyclical != 0, l0, l1, s1);
+        if (s1 != ACX_ROW_OK) {
+            st = s1;
+            fail = t;
+            break;
+        }
+        if (states_out) {
+            uint8_t* dst = reinterpret_cast<uint8_t*>(states_out) + (p * T + t) * rowb;
+            for (int k = 0; k < rowb; ++k) dst[k] = row[k];
+        }
+        if (lens_out) {
+            lens_out[2 * (p * T + t)] = (uint8_t)l0;
+            lens_out[2 * (p * T + t) + 1] = (uint8_t)l1;
+        }
+    }
+    if (final_out) {
+        uint8_t* dst = reinterpret_cast<uint8_t*>(final_out) + p * rowb;
+        for (int k = 0; k < rowb; ++k) dst[k] = row[k];
+    }
+    if (final_lens) {
+        final_lens[2 * p] = (uint8_t)l0;
+        final_lens[2 * p + 1] = (uint8_t)l1;
+    }
+    if (fail_step) fail_step[p] = fail;
+    if (status) status[p] = (uint8_t)st;
+}
+
+template <int W, int TR>
+static int launch_replay(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t P, int T, int m, int cyclical,
+                         int8_t* states_out, uint8_t* lens_out, int8_t* final_out, uint8_t* final_lens, int32_t* fail_step,
+                         uint8_t* status, cudaStream_t st) {
+    const size_t smem = (size_t)TR * ((2 * m + 7) / 8 * 8);
+    auto kern = k_path_replay<W, TR>;
+    kern<<<(unsigned)((P + TR - 1) / TR), TR, smem, st>>>(roots, actions, path_len, P, T, m, cyclical, states_out, lens_out, final_out,
+                                                        final_lens, fail_step, status);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
+}  // namespace acx
+
+using namespace acx;
+
+extern "C" int acx_path_replay(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t n_paths, int max_steps,
+                               int m, int cyclical, int8_t* states_out, uint8_t* lens_out, int8_t* final_out, uint8_t* final_lens,
+                               int32_t* fail_step, uint8_t* status, acx_stream_t stream) {
+    if (n_paths < 0 || max_steps < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH) return acx_fail(ACX_ERR_ARG, "acx_path_replay: need n_paths >= 0, max_steps >= 0, 1 <= m <= 128");
+    if (n_paths == 0) return ACX_OK;
+    if (!roots || (max_steps > 0 && !actions)) return acx_fail(ACX_ERR_ARG, "acx_path_replay: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (m <= 32) return launch_replay<1, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+    if (m <= 64) return launch_replay<2, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+    return launch_replay<4, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+}

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench_configs.py -- the other BASELINE.json configs (bench.py measures configs[1]).
 
-    python bench_configs.py [greedy] [expand] [ppo] [bfs]
+    python bench_configs.py [greedy] [expand] [expand36] [ppo] [bfs] [replay]
 
 Prints one JSON line per config.  Same timing rules as bench.py (CUDA events, warm-up, footprint > L2)."""
 import json
@@ -156,6 +156,46 @@ def cfg_ppo(dev, n=65536, T=64):
     return out
 
 
+def cfg_replay(dev, n_paths=1 << 18, steps=64):
+    """batched path replay (every intermediate state emitted), m=36."""
+    from acx import _lib
+    from acx.batch import _prep, _ptr
+
+    rows = [r for r in dataset_rows() if len(r) == 72]
+    rng = np.random.default_rng(5)
+    roots = torch.from_numpy(np.stack([rows[i] for i in rng.integers(0, len(rows), size=n_paths)])).to(dev)
+    acts = torch.from_numpy(rng.integers(0, 12, size=(n_paths, steps)).astype(np.uint8)).to(dev)
+    states = torch.empty((n_paths, steps, 72), dtype=torch.int8, device=dev)
+    lens = torch.empty((n_paths, steps, 2), dtype=torch.uint8, device=dev)
+    final = torch.empty((n_paths, 72), dtype=torch.int8, device=dev)
+    flen = torch.empty((n_paths, 2), dtype=torch.uint8, device=dev)
+    fail = torch.empty((n_paths,), dtype=torch.int32, device=dev)
+    status = torch.empty((n_paths,), dtype=torch.uint8, device=dev)
+    stream = _prep(dev)
+    L = _lib.lib()
+
+    def run():
+        _lib.check(L.acx_path_replay(_ptr(roots), _ptr(acts), 0, n_paths, steps, 36, 1, _ptr(states), _ptr(lens), _ptr(final),
+                                     _ptr(flen), _ptr(fail), _ptr(status), stream), "acx_path_replay")
+
+    for _ in range(3):
+        run()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    alg = n_paths * steps * (72 + 2 + 1)  # every state and length pair written, one action read
+    return {"config": "8(f) rank 2: path replay, %d paths x %d steps, max_relator_length=36, all intermediate states emitted" % (n_paths, steps),
+            "ms": ms, "transitions_per_s": n_paths * steps / (ms * 1e-3),
+            "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": 6538.3, "unit": "GB/s",
+                         "frac": alg / (ms * 1e-3) / 1e9 / 6538.3, "alg_bytes_per_step": 75},
+            "failed_paths": int((status != 0).sum()),
+            "reference": "one Python ACMove per step, about 1e4 per second per core (agents/training.py:74-135)"}
+
+
 if __name__ == "__main__":
     dev = torch.device("cuda:0")
     which = sys.argv[1:] or ["greedy", "expand", "ppo"]
@@ -168,6 +208,8 @@ if __name__ == "__main__":
             print(json.dumps(cfg_expand(dev, m=36, chunk=1 << 20, total=1 << 26)))
         elif w == "ppo":
             print(json.dumps(cfg_ppo(dev)))
+        elif w == "replay":
+            print(json.dumps(cfg_replay(dev)))
         elif w == "bfs":
             import bench_bfs
             print(json.dumps(bench_bfs.run(dev)))

@@ -214,6 +214,18 @@ int acx_bfs_window_partition(const int64_t* gid, int64_t n, int64_t lo, int64_t 
                              const int64_t* offsets, uint64_t* cursor, int64_t first, int64_t* loc_out, int64_t* gid_out,
                              int phase, acx_stream_t stream);
 
+/* Batched path replay: ACMove along a time axis, every intermediate state emitted (replaces the Python loops of
+ * agents/training.py:74-135 replay_final_state / actions_to_path, value_search/replay_path.py:107-160,
+ * value_search/data_extraction.py:53-190).  Path p applies actions[p, 0 .. path_len[p]) (0-based move ids,
+ * path_len NULL = max_steps for all) to roots[p]:
+ *   states_out int8 [n_paths, max_steps, 2m] and lens_out uint8 [n_paths, max_steps, 2] after every step (nullable),
+ *   final_out int8 [n_paths, 2m], final_lens uint8 [n_paths, 2], status uint8 [n_paths] (ACX_ROW_STATUS_*),
+ *   fail_step int32 [n_paths] = the step that stopped the path (-1: none).  A step that empties a relator -- where
+ *   the reference raises AssertionError (utils.py:264-266) -- stops the path with the state before that step. */
+int acx_path_replay(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t n_paths, int max_steps, int m,
+                    int cyclical, int8_t* states_out, uint8_t* lens_out, int8_t* final_out, uint8_t* final_lens,
+                    int32_t* fail_step, uint8_t* status, acx_stream_t stream);
+
 /* Peer memory (CUDA IPC): a receive buffer the other ranks of one NVLink domain write into directly, so that
  * acx_bfs_expand_bucket IS the all-to-all (stores over NVLink from inside the kernel, no staging, no collective). */
 int acx_peer_alloc(int64_t bytes, void** ptr);
