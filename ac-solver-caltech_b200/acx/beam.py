@@ -1,0 +1,144 @@
+"""beam_search on the GPU: value_search/value_guided_search.py:417-561.
+
+The reference expands the beam one ACMove at a time in Python, moves every child to numpy features / token ids and
+back to torch for scoring.  Here one step is
+
+    gather beam rows -> acx_expand12 (beam x 12 children) -> acx_bfs_probe (success test before the visited test,
+    first discovery in (beam rank, action) order) -> budget cut per child (:519-522) -> acx_bfs_commit ->
+    acx_rows_features / token ids on the device -> the caller's torch model -> stable top-k
+
+with the visited set, the node store and the scores resident in HBM.  Same signature and return value as the
+reference (`solved, path, stats`); `solution_cache` (a Python dict probed with rotation variants, :457-461,
+:500-509) is host-side memoisation and is not supported here.
+"""
+import time
+
+import numpy as np
+import torch
+
+from . import _lib
+from .batch import _prep, _ptr
+from .bfs import U64_MAX, _next_pow2
+
+
+def features(rows):
+    """compute_features (value_search/feature_extraction.py:11-91) for int8 CUDA rows [N, 2m] -> float32 [N, 14]"""
+    n, rowb = rows.shape
+    stream = _prep(rows.device)
+    out = torch.empty((n, 14), dtype=torch.float32, device=rows.device)
+    _lib.check(_lib.lib().acx_rows_features(_ptr(rows.contiguous()), n, rowb // 2, _ptr(out), stream), "acx_rows_features")
+    return out
+
+
+def score_states_mlp(rows, model, feat_mean, feat_std):
+    """_score_states_mlp (value_guided_search.py:49-63) without the numpy hop; float32 scores on the device"""
+    f = features(rows)
+    mean = torch.as_tensor(np.asarray(feat_mean, dtype=np.float32), device=rows.device)
+    std = torch.as_tensor(np.asarray(feat_std, dtype=np.float32), device=rows.device)
+    with torch.no_grad():
+        return torch.expm1(model((f - mean) / std).squeeze(-1))
+
+
+def score_states_seq(rows, model, max_state_dim):
+    """_score_states_seq (value_guided_search.py:66-83): token ids = letter + 2, padding token 2"""
+    n, rowb = rows.shape
+    tok = torch.full((n, max_state_dim), 2, dtype=torch.long, device=rows.device)
+    tok[:, :rowb] = rows.to(torch.long) + 2
+    with torch.no_grad():
+        return torch.expm1(model(tok).squeeze(-1))
+
+
+def beam_search(presentation, model, architecture="mlp", feat_mean=None, feat_std=None, beam_width=50,
+                max_nodes_to_explore=10000, device="cuda:0", cyclically_reduce_after_moves=False, verbose=False,
+                solution_cache=None, time_limit=None):
+    """Returns (solved, path, stats): path = [(action, total_length), ...] without a root sentinel (:89-96),
+    stats = {'nodes_explored', 'steps'} (:496-497, :560)."""
+    if solution_cache is not None:
+        raise NotImplementedError("solution_cache is host-side memoisation of the reference driver; not part of the GPU path")
+    root = np.ascontiguousarray(np.asarray(presentation), dtype=np.int8)
+    rowb = len(root)
+    m = rowb // 2
+    if rowb % 4:
+        raise ValueError("beam_search on the GPU needs an even max_relator_length")
+    dev = torch.device(device)
+    stream = _prep(dev)
+    L = _lib.lib()
+    budget = int(max_nodes_to_explore)
+    cyc = int(bool(cyclically_reduce_after_moves))
+    W = int(beam_width)
+    cap = max(budget, 1) + 16
+    tcap = _next_pow2(2 * (cap + 12 * W))
+    nodes = torch.zeros((cap, rowb), dtype=torch.int8, device=dev)
+    parent = torch.full((cap,), -1, dtype=torch.int64, device=dev)
+    action = torch.zeros((cap,), dtype=torch.uint8, device=dev)
+    total = torch.zeros((cap,), dtype=torch.int16, device=dev)
+    table = torch.zeros((tcap,), dtype=torch.int64, device=dev)
+    nodes[0].copy_(torch.from_numpy(root))
+    total[0] = int(np.count_nonzero(root))
+    _lib.check(L.acx_bfs_seed(_ptr(nodes), m, _ptr(table), tcap, 0, stream), "acx_bfs_seed")
+
+    def path_to(node, last_action):
+        chain = []
+        while node > 0:
+            chain.append((int(action[node]), int(total[node])))
+            node = int(parent[node])
+        chain.reverse()
+        return chain + [(int(last_action), 2)]
+
+    beam = torch.zeros((1,), dtype=torch.int64, device=dev)
+    total_nodes, step = 1, 0
+    t_start = time.time()
+    while beam.numel() and total_nodes < budget:
+        if time_limit is not None and (time.time() - t_start) > time_limit:
+            if verbose:
+                print(f"Time limit ({time_limit}s) exceeded")
+            break
+        step += 1
+        F = beam.numel()
+        n = 12 * F
+        rows = nodes[beam]
+        ch = torch.empty((n, rowb), dtype=torch.int8, device=dev)
+        ln = torch.empty((n, 2), dtype=torch.uint8, device=dev)
+        st = torch.empty((n,), dtype=torch.uint8, device=dev)
+        slot = torch.empty((n,), dtype=torch.int64, device=dev)
+        is_new = torch.empty((n,), dtype=torch.uint8, device=dev)
+        mins = torch.full((2,), -1, dtype=torch.int64, device=dev)
+        _lib.check(L.acx_expand12(_ptr(rows), _ptr(ch), _ptr(ln), _ptr(st), F, m, cyc, stream), "acx_expand12")
+        _lib.check(L.acx_bfs_probe(_ptr(ch), _ptr(ln), _ptr(st), 0, n, m, _ptr(table), tcap, _ptr(nodes), _ptr(slot),
+                                   mins[0:].data_ptr(), mins[1:].data_ptr(), 0, _ptr(is_new), stream), "acx_bfs_probe")
+        cum = torch.cumsum(is_new, dim=0, dtype=torch.int64)
+        need = budget - total_nodes  # the child that brings total_nodes to the budget ends the expansion (:519-522)
+        head = torch.cat([mins, cum[-1:], torch.searchsorted(cum, torch.tensor([need], device=dev))]).cpu().numpy()
+        c_s, c_e, n_new = int(head[0]) & U64_MAX, int(head[1]) & U64_MAX, int(head[2])
+        c_b = int(head[3]) if n_new >= need else U64_MAX
+        first = min(c_s, c_e, c_b)
+        if first != U64_MAX and first == c_e:
+            raise AssertionError("a relator became empty during the search: not a valid presentation")
+        if first != U64_MAX and first == c_s:
+            before = int(cum[c_s - 1]) if c_s > 0 else 0
+            # the nodes added before the solving child exist in the reference's tree; they only matter for the count
+            stats = {"nodes_explored": total_nodes + before, "steps": step}
+            return True, path_to(int(beam[c_s // 12]), c_s % 12), stats
+        limit = n if first == U64_MAX else c_b + 1
+        excl = cum - is_new
+        _lib.check(L.acx_bfs_commit(_ptr(ch), _ptr(ln), _ptr(slot), _ptr(is_new), _ptr(excl), 0, 0, n, limit, m, _ptr(table),
+                                    _ptr(nodes), _ptr(parent), _ptr(action), total.data_ptr(), total_nodes, stream), "acx_bfs_commit")
+        added = n_new if first == U64_MAX else need
+        new_ids = torch.arange(total_nodes, total_nodes + added, device=dev)
+        parent[new_ids] = beam[parent[new_ids]]  # commit stored the beam rank; the parent is that beam entry's node
+        total_nodes += added
+        if added == 0:
+            break
+        if total_nodes >= budget:
+            break  # the reference scores this last batch and then leaves the loop without using it (:421, :526-541)
+        child_rows = nodes[new_ids]
+        if architecture == "mlp":
+            scores = score_states_mlp(child_rows, model, feat_mean, feat_std)
+        else:
+            scores = score_states_seq(child_rows, model, rowb)
+        order = torch.sort(scores.to(torch.float64), stable=True).indices  # ties keep discovery order (:540)
+        beam = new_ids[order[:W]]
+        if verbose and step % 10 == 0:
+            print(f"  Step {step}: beam_size={beam.numel()}, nodes={total_nodes}, best_score={float(scores[order[0]]):.1f}, "
+                  f"min_len={int(total[beam].min())}")
+    return False, [], {"nodes_explored": total_nodes, "steps": step}

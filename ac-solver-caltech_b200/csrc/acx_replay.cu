@@ -83,9 +83,53 @@ static int launch_replay(const int8_t* roots, const uint8_t* actions, const int3
     return ACX_OK;
 }
 
+// The 14 handcrafted features of value_search/feature_extraction.py:11-91, one thread per row, float32 out.
+// Counts run over the first len(r) letters of each relator (:50-61); the two ratios are computed in double and
+// rounded once to float32, as numpy does when it builds the float32 array from Python floats (:68-91).
+__global__ void k_rows_features(const int8_t* rows, int64_t n, int m, float* out) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int8_t* r = rows + j * 2 * m;
+    int len[2] = {0, 0};
+    for (int k = 0; k < m; ++k) {
+        len[0] += r[k] != 0;
+        len[1] += r[m + k] != 0;
+    }
+    int cnt[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};  // x, x^-1, y, y^-1
+    for (int i = 0; i < 2; ++i)
+        for (int k = 0; k < len[i]; ++k) {
+            const int v = r[i * m + k];
+            cnt[i][0] += v == 1;
+            cnt[i][1] += v == -1;
+            cnt[i][2] += v == 2;
+            cnt[i][3] += v == -2;
+        }
+    const int total = len[0] + len[1];
+    const int mn = min(len[0], len[1]), mx = max(len[0], len[1]);
+    float* o = out + j * 14;
+    o[0] = (float)total;
+    o[1] = (float)len[0];
+    o[2] = (float)len[1];
+    for (int i = 0; i < 2; ++i)
+        for (int c = 0; c < 4; ++c) o[3 + 4 * i + c] = (float)cnt[i][c];
+    o[11] = (float)((cnt[0][0] - cnt[0][1]) + (cnt[1][0] - cnt[1][1]));
+    o[12] = total > 0 ? (float)((double)len[0] / (double)total) : 0.5f;
+    o[13] = mn > 0 ? (float)((double)mx / (double)mn) : (float)mx;
+}
+
 }  // namespace acx
 
 using namespace acx;
+
+extern "C" int acx_rows_features(const int8_t* rows, int64_t n, int m, float* features_out, acx_stream_t stream) {
+    if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH) return acx_fail(ACX_ERR_ARG, "acx_rows_features: need n >= 0, 1 <= m <= 128");
+    if (n == 0) return ACX_OK;
+    if (!rows || !features_out) return acx_fail(ACX_ERR_ARG, "acx_rows_features: null pointer");
+    k_rows_features<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(rows, n, m, features_out);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
 
 extern "C" int acx_path_replay(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t n_paths, int max_steps,
                                int m, int cyclical, int8_t* states_out, uint8_t* lens_out, int8_t* final_out, uint8_t* final_lens,

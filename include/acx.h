@@ -226,6 +226,10 @@ int acx_path_replay(const int8_t* roots, const uint8_t* actions, const int32_t* 
                     int cyclical, int8_t* states_out, uint8_t* lens_out, int8_t* final_out, uint8_t* final_lens,
                     int32_t* fail_step, uint8_t* status, acx_stream_t stream);
 
+/* The 14 handcrafted value-network features of value_search/feature_extraction.py:11-91, float32 [n, 14], computed
+ * where the rows already are (removes the numpy hop of value_guided_search.py:49-63). */
+int acx_rows_features(const int8_t* rows, int64_t n, int m, float* features_out, acx_stream_t stream);
+
 /* Peer memory (CUDA IPC): a receive buffer the other ranks of one NVLink domain write into directly, so that
  * acx_bfs_expand_bucket IS the all-to-all (stores over NVLink from inside the kernel, no staging, no collective). */
 int acx_peer_alloc(int64_t bytes, void** ptr);

@@ -1,0 +1,156 @@
+"""GPU parity of acx.beam against a literal restatement of the reference's beam_search
+(value_search/value_guided_search.py:417-561) that uses the oracle's ACMove, numpy compute_features
+(value_search/feature_extraction.py:11-91) and the same torch model on the same device for scoring."""
+import numpy as np
+import pytest
+
+from helpers import AK2, AK3, dataset_rows, pad_row, random_rows, repad
+
+pytestmark = pytest.mark.gpu
+
+
+def _features_np(p, m):
+    r1, r2 = p[:m], p[m:]
+    l1, l2 = int(np.count_nonzero(r1)), int(np.count_nonzero(r2))
+    tot = l1 + l2
+    a, b = r1[:l1], r2[:l2]
+    c = [int(np.sum(a == v)) for v in (1, -1, 2, -2)] + [int(np.sum(b == v)) for v in (1, -1, 2, -2)]
+    ex = (c[0] - c[1]) + (c[4] - c[5])
+    ratio = l1 / tot if tot > 0 else 0.5
+    mn, mx = min(l1, l2), max(l1, l2)
+    mm = mx / mn if mn > 0 else mx
+    return np.array([tot, l1, l2] + c + [ex, ratio, mm], dtype=np.float32)
+
+
+def _score(states, model, arch, mean, std, dev, dim):
+    import torch
+
+    if arch == "mlp":
+        f = np.stack([_features_np(s, len(s) // 2) for s in states])
+        f = (f - mean) / std
+        t = torch.tensor(f, dtype=torch.float32, device=dev)
+    else:
+        tok = np.full((len(states), dim), 2, dtype=np.int64)
+        for k, s in enumerate(states):
+            tok[k, : len(s)] = s.astype(np.int64) + 2
+        t = torch.tensor(tok, dtype=torch.long, device=dev)
+    with torch.no_grad():
+        return torch.expm1(model(t).squeeze(-1)).cpu().numpy().tolist()
+
+
+def _beam_oracle(oracle, presentation, model, arch, mean, std, width, budget, dev, cyc):
+    presentation = np.array(presentation, dtype=np.int8)
+    m = len(presentation) // 2
+    l1, l2 = int(np.count_nonzero(presentation[:m])), int(np.count_nonzero(presentation[m:]))
+    parent_map = {0: (None, l1 + l2, None)}
+    next_id = 1
+    beam = [(presentation.copy(), [l1, l2], 0)]
+    visited = {tuple(presentation)}
+    total_nodes, step = 1, 0
+
+    def recon(nid):
+        path = []
+        while nid is not None:
+            a, ln, par = parent_map[nid]
+            if par is None:
+                break
+            path.append((a, ln))
+            nid = par
+        path.reverse()
+        return path
+
+    while beam and total_nodes < budget:
+        step += 1
+        children = []
+        for state, wl, pid in beam:
+            for action in range(12):
+                ns, nl = oracle.ACMove(action, state, m, wl, cyc)
+                new_length = int(sum(nl))
+                tup = tuple(ns)
+                if new_length == 2:
+                    return True, recon(pid) + [(action, new_length)], {"nodes_explored": total_nodes, "steps": step}
+                if tup not in visited:
+                    visited.add(tup)
+                    total_nodes += 1
+                    parent_map[next_id] = (action, new_length, pid)
+                    children.append((ns, nl, next_id))
+                    next_id += 1
+                    if total_nodes >= budget:
+                        break
+            if total_nodes >= budget:
+                break
+        if not children:
+            break
+        scores = _score([c[0] for c in children], model, arch, mean, std, dev, len(presentation))
+        scored = sorted(zip(scores, range(len(children))), key=lambda x: x[0])
+        beam = [children[k] for _, k in scored[:width]]
+    return False, [], {"nodes_explored": total_nodes, "steps": step}
+
+
+def _models(dev):
+    import torch
+
+    torch.manual_seed(7)
+    mlp = torch.nn.Sequential(torch.nn.Linear(14, 32), torch.nn.ReLU(), torch.nn.Linear(32, 1)).to(dev).eval()
+
+    class Seq(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = torch.nn.Embedding(5, 8)
+            self.conv = torch.nn.Conv1d(8, 8, 3, padding=1)
+            self.out = torch.nn.Linear(8, 1)
+
+        def forward(self, t):
+            x = self.emb(t).transpose(1, 2)
+            return self.out(torch.relu(self.conv(x)).mean(dim=2))
+
+    return mlp, Seq().to(dev).eval()
+
+
+def test_features_vs_numpy(cuda):
+    import torch
+
+    from acx.beam import features
+
+    rng = np.random.default_rng(3)
+    for m in (7, 18, 36, 128):
+        rows = random_rows(rng, 600, m, kinds=(0, 1, 2, 3, 4))
+        rows[0] = 0
+        rows[1, m:] = 0
+        got = features(torch.from_numpy(rows).to(cuda)).cpu().numpy()
+        want = np.stack([_features_np(r, m) for r in rows])
+        assert got.dtype == np.float32 and (got.view(np.uint32) == want.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("arch", ["mlp", "seq", "len"])
+def test_beam_search_vs_reference_restatement(cuda, oracle, golden_dir, arch):
+    import torch
+
+    from acx.beam import beam_search
+
+    mlp, seq = _models(cuda)
+    model = mlp if arch == "mlp" else seq
+    if arch == "len":  # score = a monotone function of the total length: a beam that actually solves things
+        model = torch.nn.Linear(14, 1).to(cuda).eval()
+        with torch.no_grad():
+            model.weight.zero_()
+            model.bias.zero_()
+            model.weight[0, 0] = 1.0
+    mean = np.linspace(1.0, 14.0, 14).astype(np.float32)
+    std = np.linspace(2.0, 5.0, 14).astype(np.float32)
+    rows = dataset_rows(golden_dir)
+    rng = np.random.default_rng(11)
+    cases = [(repad(AK2, 8), 4, 300, False), (pad_row(AK3[0], AK3[1], 36), 50, 3000, True)]
+    for k in rng.choice(len(rows), size=10, replace=False):
+        cases.append((rows[int(k)], int(rng.choice([1, 5, 50])), int(rng.choice([2, 40, 700, 2500])), bool(rng.integers(0, 2))))
+    if arch == "len":
+        cases += [(rows[k], 10, 2000, bool(k % 2)) for k in range(0, 40, 4)]
+    a = "seq" if arch == "seq" else "mlp"
+    n_solved = 0
+    for row, width, budget, cyc in cases:
+        want = _beam_oracle(oracle, row, model, a, mean, std, width, budget, cuda, cyc)
+        got = beam_search(row, model, architecture=a, feat_mean=mean, feat_std=std, beam_width=width,
+                          max_nodes_to_explore=budget, device=str(cuda), cyclically_reduce_after_moves=cyc)
+        assert got == want, (len(row), width, budget, cyc)
+        n_solved += int(want[0])
+    assert n_solved >= 1 or arch != "len"
