@@ -110,6 +110,10 @@ __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t nti
         mbar_fence_init();
     }
     __syncthreads();
+    // Programmatic dependent launch: the CTAs of the next step may become resident and run the prologue above while
+    // this step's last CTAs drain; nothing of the previous step is read or written before the wait below.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     const int64_t first = blockIdx.x, stride = gridDim.x;
     const int8_t* gin = p.in + p.row0 * ROWB;
@@ -278,8 +282,21 @@ static int launch_tma(const StepParams& p, int64_t ntiles, cudaStream_t st) {
         ctas_per_sm[dev] = occ > 0 ? occ : 1;
     }
     const int64_t grid = std::min<int64_t>(ntiles, (int64_t)sm_count() * ctas_per_sm[dev]);
-    kern<<<(unsigned)grid, TR, smem, st>>>(p, ntiles);
-    ACX_CUDA(cudaGetLastError());
+    static const int pdl = [] {
+        const char* e = getenv("ACX_PDL");
+        return e ? atoi(e) : 1;
+    }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(TR);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    ACX_CUDA(cudaLaunchKernelEx(&cfg, kern, p, ntiles));
     return ACX_OK;
 }
 
