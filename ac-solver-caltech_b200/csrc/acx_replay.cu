@@ -16,52 +16,84 @@
 
 namespace acx {
 
-template <int W, int TR>
+// MS > 0: static width (rows of 2*MS bytes, 8-byte multiples); MS == 0: any width.
+// A warp owns 32 paths.  After every step the 32 rows are written out cooperatively (consecutive lanes write
+// consecutive 8-byte words of one row: whole 32-byte sectors instead of 32 scattered words per store).
+template <int W, int MS, int TR>
 __global__ void __launch_bounds__(TR) k_path_replay(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t P,
-                                                    int T, int m, int cyclical, int8_t* states_out, uint8_t* lens_out,
+                                                    int T, int m_rt, int cyclical, int8_t* states_out, uint8_t* lens_out,
                                                     int8_t* final_out, uint8_t* final_lens, int32_t* fail_step, uint8_t* status) {
     extern __shared__ __align__(16) uint8_t smem[];
+    const int m = MS ? MS : m_rt;
     const int rowb = 2 * m, pitch = (rowb + 7) / 8 * 8;
-    const int64_t p = (int64_t)blockIdx.x * TR + threadIdx.x;
-    if (p >= P) return;
-    uint8_t* row = smem + (size_t)threadIdx.x * pitch;
-    const uint8_t* src = reinterpret_cast<const uint8_t*>(roots) + p * rowb;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t p0 = ((int64_t)blockIdx.x * (TR / 32) + wid) * 32;  // first path of this warp
+    if (p0 >= P) return;
+    const int64_t p = p0 + lane;
+    const bool valid = p < P;
+    uint8_t* wrows = smem + (size_t)wid * 32 * pitch;
+    uint8_t* row = wrows + (size_t)lane * pitch;
+    const bool words = (rowb % 8 == 0) && ((((uintptr_t)roots | (uintptr_t)states_out | (uintptr_t)final_out) & 7u) == 0);
     int l0 = 0, l1 = 0;
-    for (int k = 0; k < rowb; ++k) {
-        const uint8_t v = src[k];
-        row[k] = v;
-        if (v) (k < m ? l0 : l1) += 1;
+    if (valid) {
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(roots) + p * rowb;
+        for (int k = 0; k < rowb; ++k) {
+            const uint8_t v = src[k];
+            row[k] = v;
+            if (v) (k < m ? l0 : l1) += 1;
+        }
     }
-    const int n = min(path_len ? path_len[p] : T, T);
+    const int n = valid ? min(path_len ? path_len[p] : T, T) : 0;
+    int nmax = n;
+    for (int o = 16; o; o >>= 1) nmax = max(nmax, __shfl_xor_sync(0xFFFFFFFFu, nmax, o));
     uint32_t st = ACX_ROW_OK;
     int fail = -1;
-    for (int t = 0; t < n; ++t) {
-        const int a = actions[p * T + t];
-        if (a >= 12) {
-            st = ACX_ROW_INVALID_INPUT;
-            fail = t;
-            break;
-        }
-        uint32_t s1 = ACX_ROW_OK;
-        if constexpr (W <= 2) acmove_row64<0>(row, m, a, cyclical != 0, l0, l1, s1);
-        else acmove_row<W, 0>(row, row, m, a, cyclical != 0, l0, l1, s1);
-        if (s1 != ACX_ROW_OK) {
-            st = s1;
-            fail = t;
-            break;
+    for (int t = 0; t < nmax; ++t) {
+        bool emit = false;
+        if (t < n && fail < 0) {
+            const int a = actions[p * T + t];
+            uint32_t s1 = ACX_ROW_OK;
+            if (a >= 12) {
+                s1 = ACX_ROW_INVALID_INPUT;
+            } else {
+                if constexpr (W <= 2) acmove_row64<MS>(row, m, a, cyclical != 0, l0, l1, s1);
+                else acmove_row<W, MS>(row, row, m, a, cyclical != 0, l0, l1, s1);
+            }
+            if (s1 != ACX_ROW_OK) {
+                st = s1;
+                fail = t;
+            } else {
+                emit = true;
+                if (lens_out) *reinterpret_cast<uchar2*>(lens_out + 2 * (p * T + t)) = make_uchar2((uint8_t)l0, (uint8_t)l1);
+            }
         }
         if (states_out) {
-            uint8_t* dst = reinterpret_cast<uint8_t*>(states_out) + (p * T + t) * rowb;
-            for (int k = 0; k < rowb; ++k) dst[k] = row[k];
-        }
-        if (lens_out) {
-            lens_out[2 * (p * T + t)] = (uint8_t)l0;
-            lens_out[2 * (p * T + t) + 1] = (uint8_t)l1;
+            const unsigned em = __ballot_sync(0xFFFFFFFFu, emit);
+            __syncwarp();
+            uint8_t* base = reinterpret_cast<uint8_t*>(states_out);
+            if (words) {
+                const int cw = rowb / 8;
+                for (int c = lane; c < 32 * cw; c += 32) {
+                    const int r = c / cw, k = c - r * cw;
+                    if ((em >> r) & 1u)
+                        *reinterpret_cast<uint2*>(base + ((p0 + r) * T + t) * rowb + 8 * k) =
+                            *reinterpret_cast<const uint2*>(wrows + (size_t)r * pitch + 8 * k);
+                }
+            } else if (emit) {
+                uint8_t* dst = base + (p * T + t) * rowb;
+                for (int k = 0; k < rowb; ++k) dst[k] = row[k];
+            }
+            __syncwarp();
         }
     }
+    if (!valid) return;
     if (final_out) {
         uint8_t* dst = reinterpret_cast<uint8_t*>(final_out) + p * rowb;
-        for (int k = 0; k < rowb; ++k) dst[k] = row[k];
+        if (words) {
+            for (int k = 0; k < rowb / 8; ++k) reinterpret_cast<uint2*>(dst)[k] = reinterpret_cast<const uint2*>(row)[k];
+        } else {
+            for (int k = 0; k < rowb; ++k) dst[k] = row[k];
+        }
     }
     if (final_lens) {
         final_lens[2 * p] = (uint8_t)l0;
@@ -71,12 +103,12 @@ __global__ void __launch_bounds__(TR) k_path_replay(const int8_t* roots, const u
     if (status) status[p] = (uint8_t)st;
 }
 
-template <int W, int TR>
+template <int W, int MS, int TR>
 static int launch_replay(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t P, int T, int m, int cyclical,
                          int8_t* states_out, uint8_t* lens_out, int8_t* final_out, uint8_t* final_lens, int32_t* fail_step,
                          uint8_t* status, cudaStream_t st) {
     const size_t smem = (size_t)TR * ((2 * m + 7) / 8 * 8);
-    auto kern = k_path_replay<W, TR>;
+    auto kern = k_path_replay<W, MS, TR>;
     kern<<<(unsigned)((P + TR - 1) / TR), TR, smem, st>>>(roots, actions, path_len, P, T, m, cyclical, states_out, lens_out, final_out,
                                                         final_lens, fail_step, status);
     ACX_CUDA(cudaGetLastError());
@@ -138,7 +170,8 @@ extern "C" int acx_path_replay(const int8_t* roots, const uint8_t* actions, cons
     if (n_paths == 0) return ACX_OK;
     if (!roots || (max_steps > 0 && !actions)) return acx_fail(ACX_ERR_ARG, "acx_path_replay: null pointer");
     cudaStream_t st = (cudaStream_t)stream;
-    if (m <= 32) return launch_replay<1, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
-    if (m <= 64) return launch_replay<2, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
-    return launch_replay<4, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+    if (m == 36) return launch_replay<2, 36, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+    if (m <= 32) return launch_replay<1, 0, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+    if (m <= 64) return launch_replay<2, 0, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+    return launch_replay<4, 0, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
 }
