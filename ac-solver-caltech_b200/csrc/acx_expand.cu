@@ -9,6 +9,7 @@
 //                    children are staged per warp and written back with coalesced vector stores.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/acx.h"
@@ -257,7 +258,21 @@ extern "C" int acx_expand12(const int8_t* parents, int8_t* children, uint8_t* ch
     p.cyclical = cyclical;
     cudaStream_t st = (cudaStream_t)stream;
     const bool aligned = (((uintptr_t)parents | (uintptr_t)children) & 15u) == 0;
-    if (aligned && m == 36) return launch_expand_warp<2, 36, 4, 4>(p, st);
+    if (aligned && m == 36) {
+        static const int cfg = [] {  // tuning knob: ACX_EXPAND36 = GM*10 + WARPS
+            const char* e = getenv("ACX_EXPAND36");
+            return e ? atoi(e) : 48;
+        }();
+        switch (cfg) {
+            case 24: return launch_expand_warp<2, 36, 2, 4>(p, st);
+            case 28: return launch_expand_warp<2, 36, 2, 8>(p, st);
+            case 42: return launch_expand_warp<2, 36, 4, 2>(p, st);
+            case 64: return launch_expand_warp<2, 36, 6, 4>(p, st);
+            case 34: return launch_expand_warp<2, 36, 3, 4>(p, st);
+            case 44: return launch_expand_warp<2, 36, 4, 4>(p, st);
+            default: return launch_expand_warp<2, 36, 4, 8>(p, st);
+        }
+    }
     if (aligned && m == 128) return launch_expand_warp<4, 128, 1, 4>(p, st);
     if (m <= 32) return launch_expand_simple<1, 8>(p, st);
     if (m <= 64) return launch_expand_simple<2, 8>(p, st);
