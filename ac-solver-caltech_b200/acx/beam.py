@@ -142,3 +142,112 @@ def beam_search(presentation, model, architecture="mlp", feat_mean=None, feat_st
             print(f"  Step {step}: beam_size={beam.numel()}, nodes={total_nodes}, best_score={float(scores[order[0]]):.1f}, "
                   f"min_len={int(total[beam].min())}")
     return False, [], {"nodes_explored": total_nodes, "steps": step}
+
+
+def value_guided_greedy_search(presentation, model=None, architecture="mlp", feat_mean=None, feat_std=None,
+                               max_nodes_to_explore=10000, device="cuda:0", use_length_priority=False,
+                               cyclically_reduce_after_moves=False, verbose=False, solution_cache=None, time_limit=None):
+    """value_search/value_guided_search.py:253-414: best-first search on V(P) (or on the total length).
+
+    The pops are sequential (the heap lives on the host, as in the reference); each pop is one `acx_expand12` of the
+    popped row, one `acx_bfs_probe` against the resident visited set, one device-side scoring batch of the children
+    and one `acx_bfs_commit`.  Quirks kept: a child is "new" when its state was not in the map BEFORE this pop, so
+    two equal children of one pop are both pushed (:375-376, :392-401); the budget test runs after each pop (:403).
+    Returns (solved, path, {'nodes_explored', 'min_length'})."""
+    import heapq
+
+    if solution_cache is not None:
+        raise NotImplementedError("solution_cache is host-side memoisation of the reference driver; not part of the GPU path")
+    root = np.ascontiguousarray(np.asarray(presentation), dtype=np.int8)
+    rowb = len(root)
+    m = rowb // 2
+    if rowb % 4:
+        raise ValueError("value_guided_greedy_search on the GPU needs an even max_relator_length")
+    dev = torch.device(device)
+    stream = _prep(dev)
+    L = _lib.lib()
+    budget = int(max_nodes_to_explore)
+    cyc = int(bool(cyclically_reduce_after_moves))
+    cap = 2 * (max(budget, 1) + 16)  # equal children of one pop are stored twice
+    tcap = _next_pow2(2 * (cap + 12))
+    nodes = torch.zeros((cap, rowb), dtype=torch.int8, device=dev)
+    parent_t = torch.full((cap,), -1, dtype=torch.int64, device=dev)  # scratch for acx_bfs_commit (the tree lives on the host)
+    action_t = torch.zeros((cap,), dtype=torch.uint8, device=dev)
+    total_t = torch.zeros((cap,), dtype=torch.int16, device=dev)
+    table = torch.zeros((tcap,), dtype=torch.int64, device=dev)
+    nodes[0].copy_(torch.from_numpy(root))
+    _lib.check(L.acx_bfs_seed(_ptr(nodes), m, _ptr(table), tcap, 0, stream), "acx_bfs_seed")
+    total0 = int(np.count_nonzero(root))
+    parent_map = {0: (None, total0, None)}
+
+    def score(rows):
+        if architecture == "mlp":
+            return score_states_mlp(rows, model, feat_mean, feat_std).cpu().numpy().tolist()
+        return score_states_seq(rows, model, rowb).cpu().numpy().tolist()
+
+    def path_to(nid):
+        path = []
+        while nid is not None:
+            a, ln, par = parent_map[nid]
+            if par is None:
+                break
+            path.append((a, ln))
+            nid = par
+        path.reverse()
+        return path
+
+    init_priority = float(total0) if use_length_priority else score(nodes[0:1])[0]
+    heap = [(init_priority, 0, 0)]
+    next_id, n_states, min_length = 1, 1, total0
+    ch = torch.empty((12, rowb), dtype=torch.int8, device=dev)
+    ln = torch.empty((12, 2), dtype=torch.uint8, device=dev)
+    st = torch.empty((12,), dtype=torch.uint8, device=dev)
+    slot = torch.empty((12,), dtype=torch.int64, device=dev)
+    is_new = torch.empty((12,), dtype=torch.uint8, device=dev)
+    mins = torch.empty((2,), dtype=torch.int64, device=dev)
+    t_start = time.time()
+    while heap:
+        if time_limit is not None and (time.time() - t_start) > time_limit:
+            if verbose:
+                print(f"Time limit ({time_limit}s) exceeded")
+            break
+        _, path_length, cur = heapq.heappop(heap)
+        mins.fill_(-1)
+        _lib.check(L.acx_expand12(nodes[cur].data_ptr(), _ptr(ch), _ptr(ln), _ptr(st), 1, m, cyc, stream), "acx_expand12")
+        _lib.check(L.acx_bfs_probe(_ptr(ch), _ptr(ln), _ptr(st), 0, 12, m, _ptr(table), tcap, _ptr(nodes), _ptr(slot),
+                                   mins[0:].data_ptr(), mins[1:].data_ptr(), 0, _ptr(is_new), stream), "acx_bfs_probe")
+        h = torch.cat([ln.to(torch.int64).sum(dim=1), st.to(torch.int64), slot, is_new.to(torch.int64)]).tolist()
+        tot, stat, slots, news = h[0:12], h[12:24], h[24:36], h[36:48]
+        kids = []
+        for a in range(12):
+            if stat[a]:
+                raise AssertionError("a relator became empty during the search: not a valid presentation")
+            if tot[a] < min_length:
+                min_length = tot[a]
+                if verbose:
+                    print(f"New min length: {min_length} (nodes: {n_states})")
+            if tot[a] == 2:
+                return True, path_to(cur) + [(a, 2)], {"nodes_explored": n_states, "min_length": min_length}
+            if slots[a] >= 0:
+                kids.append(a)
+        if kids:
+            idx = torch.tensor(kids, device=dev)
+            ids = torch.arange(next_id, next_id + len(kids), device=dev)
+            nodes[ids] = ch[idx]
+            scores = [tot[a] for a in kids] if use_length_priority else score(nodes[next_id: next_id + len(kids)])
+            rank = torch.zeros((12,), dtype=torch.int64, device=dev)
+            rank[idx] = torch.arange(len(kids), device=dev)
+            _lib.check(L.acx_bfs_commit(_ptr(ch), _ptr(ln), _ptr(slot), _ptr(is_new), _ptr(rank), 0, 0, 12, 12, m, _ptr(table),
+                                        _ptr(nodes), _ptr(parent_t), _ptr(action_t), total_t.data_ptr(), next_id, stream),
+                       "acx_bfs_commit")
+            for k, a in enumerate(kids):
+                nid = next_id + k
+                parent_map[nid] = (a, tot[a], cur)
+                heapq.heappush(heap, (scores[k], path_length + 1, nid))
+                n_states += news[a]
+            next_id += len(kids)
+        if n_states >= budget:
+            if verbose:
+                print(f"Budget exhausted: {n_states} nodes explored")
+            break
+    return False, [], {"nodes_explored": n_states, "min_length": min_length}

@@ -154,3 +154,84 @@ def test_beam_search_vs_reference_restatement(cuda, oracle, golden_dir, arch):
         assert got == want, (len(row), width, budget, cyc)
         n_solved += int(want[0])
     assert n_solved >= 1 or arch != "len"
+
+
+def _vgreedy_oracle(oracle, presentation, model, arch, mean, std, budget, dev, use_len, cyc):
+    """literal restatement of value_guided_greedy_search (value_guided_search.py:253-414) without the cache"""
+    import heapq
+
+    presentation = np.array(presentation, dtype=np.int8)
+    m = len(presentation) // 2
+    wl = [int(np.count_nonzero(presentation[:m])), int(np.count_nonzero(presentation[m:]))]
+    total0 = sum(wl)
+    init = float(total0) if use_len else _score([presentation], model, arch, mean, std, dev, len(presentation))[0]
+    parent_map = {0: (None, total0, None)}
+    next_id = 1
+    state_to_id = {tuple(presentation): 0}
+    heap = [(init, 0, 0, tuple(presentation), tuple(wl))]
+    min_length = total0
+
+    def recon(nid):
+        path = []
+        while nid is not None:
+            a, ln, par = parent_map[nid]
+            if par is None:
+                break
+            path.append((a, ln))
+            nid = par
+        path.reverse()
+        return path
+
+    while heap:
+        _, plen, cur, state_tuple, wl_tuple = heapq.heappop(heap)
+        state = np.array(state_tuple, dtype=np.int8)
+        children = []
+        for action in range(12):
+            ns, nl = oracle.ACMove(action, state, m, list(wl_tuple), cyc)
+            new_length = int(sum(nl))
+            tup = tuple(ns)
+            min_length = min(min_length, new_length)
+            if new_length == 2:
+                return True, recon(cur) + [(action, new_length)], {"nodes_explored": len(state_to_id), "min_length": min_length}
+            if tup not in state_to_id:
+                children.append((ns, nl, action, new_length, tup))
+        if children and not use_len:
+            scores = _score([c[0] for c in children], model, arch, mean, std, dev, len(presentation))
+        else:
+            scores = [c[3] for c in children]
+        for (ns, nl, action, new_length, tup), score in zip(children, scores):
+            nid = next_id
+            next_id += 1
+            parent_map[nid] = (action, new_length, cur)
+            state_to_id[tup] = nid
+            heapq.heappush(heap, (score, plen + 1, nid, tup, tuple(nl)))
+        if len(state_to_id) >= budget:
+            break
+    return False, [], {"nodes_explored": len(state_to_id), "min_length": min_length}
+
+
+@pytest.mark.parametrize("mode", ["mlp", "seq", "length"])
+def test_value_guided_greedy_vs_reference_restatement(cuda, oracle, golden_dir, mode):
+    from acx.beam import value_guided_greedy_search
+
+    mlp, seq = _models(cuda)
+    model = {"mlp": mlp, "seq": seq, "length": None}[mode]
+    arch = "seq" if mode == "seq" else "mlp"
+    mean = np.linspace(1.0, 14.0, 14).astype(np.float32)
+    std = np.linspace(2.0, 5.0, 14).astype(np.float32)
+    rows = dataset_rows(golden_dir)
+    rng = np.random.default_rng(23)
+    cases = [(repad(AK2, 8), 400, False), (pad_row(AK3[0], AK3[1], 36), 1500, True)]
+    for k in rng.choice(len(rows), size=8, replace=False):
+        cases.append((rows[int(k)], int(rng.choice([1, 30, 500, 1500])), bool(rng.integers(0, 2))))
+    if mode == "length":
+        cases += [(rows[k], 3000, bool(k % 2)) for k in range(0, 40, 5)]
+    n_solved = 0
+    for row, budget, cyc in cases:
+        want = _vgreedy_oracle(oracle, row, model, arch, mean, std, budget, cuda, mode == "length", cyc)
+        got = value_guided_greedy_search(row, model, architecture=arch, feat_mean=mean, feat_std=std, max_nodes_to_explore=budget,
+                                         device=str(cuda), use_length_priority=(mode == "length"),
+                                         cyclically_reduce_after_moves=cyc)
+        assert got == want, (len(row), budget, cyc)
+        n_solved += int(want[0])
+    assert n_solved >= 1 or mode != "length"
