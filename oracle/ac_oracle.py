@@ -26,7 +26,7 @@ _i64p = ctypes.POINTER(ctypes.c_int64)
 
 def build(force=False):
     """Compile liboracle.so with the Makefile next to this file."""
-    srcs = [os.path.join(_HERE, f) for f in ("ac_oracle.c", "ac_search_oracle.c", "ac_oracle.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("ac_oracle.c", "ac_search_oracle.c", "barcode_oracle.c", "ac_oracle.h")]
     stale = force or not os.path.exists(_LIB_PATH) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs
     )
