@@ -52,6 +52,12 @@ _SIGNATURES = {
     "acx_peer_close": (_I32, [_PTR]),
     "acx_env_step": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _F32, _F32, _I32, _PTR]),
     "acx_rows_certify": (_I32, [_PTR, _I64, _I32, _PTR, _PTR, _PTR]),
+    "acx_graph_scan_bytes": (_I64, [_I64]),
+    "acx_graph_step": (_I32, [_PTR, _PTR]),
+    "acx_graph_pack": (_I32, [_PTR, _I64, _I32, _PTR, _I32, _PTR, _PTR, _PTR]),
+    "acx_graph_unpack": (_I32, [_PTR, _I64, _I32, _I32, _PTR, _PTR, _PTR]),
+    "acx_graph_rehash": (_I32, [_PTR, _I64, _I32, _PTR, _I64, _PTR]),
+    "acx_graph_count_instances": (_I32, [_PTR, _I64, _I32, _PTR, _I64, _PTR]),
 }
 
 

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench_configs.py -- the other BASELINE.json configs (bench.py measures configs[1]).
 
-    python bench_configs.py [greedy] [expand] [expand36] [ppo] [bfs] [replay]
+    python bench_configs.py [greedy] [expand] [expand36] [ppo] [bfs] [replay] [graph [n]] [balls]
 
 Prints one JSON line per config.  Same timing rules as bench.py (CUDA events, warm-up, footprint > L2)."""
 import json
@@ -196,6 +196,46 @@ def cfg_replay(dev, n_paths=1 << 18, steps=64):
             "reference": "one Python ACMove per step, about 1e4 per second per core (agents/training.py:74-135)"}
 
 
+def cfg_graph(dev, n_max=14):
+    """ac_bfs.cpp (classic moves) -- the whole graph of presentations of total size <= n."""
+    from acx import graph
+
+    out = []
+    for moves in ("classic", "prime"):
+        graph.ac_graph_bfs(6, moves, device=str(dev))  # warm-up (allocator, module load)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        r = graph.ac_graph_bfs(n_max, moves, device=str(dev), chunk=1 << 20)
+        dt = time.perf_counter() - t0
+        nm = 14 if moves == "classic" else 12
+        out.append({"config": "8(f) rank 3: ac_bfs %s moves, n=%d (nodes, edges and filtrations on the host at exit)" % (moves, n_max),
+                    "wall_s": dt, "nodes": len(r["sizes"]), "edges": len(r["edges"]), "levels": len(r["levels"]),
+                    "nodes_per_s": len(r["sizes"]) / dt, "moves_per_s": nm * len(r["sizes"]) / dt,
+                    "reference": "compiled ac_bfs.cpp (g++ -O2), classic: n=12 31.7 s, n=14 407 s (7199908 nodes, 20922303 edges) "
+                                 "on one core of the build container"})
+    return out
+
+
+def cfg_balls(dev, radius=5):
+    """neibourhoods.cpp -- radius-5 ball sizes around all 1190 Miller-Schupp presentations."""
+    from acx import graph
+
+    rows = [r.tolist() for r in dataset_rows()]
+    out = []
+    graph.neighbourhood_sizes(rows[:4], 3, True, device=str(dev))
+    for classic in (True, False):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        sizes = graph.neighbourhood_sizes(rows, radius, classic, device=str(dev), chunk=1 << 20)
+        dt = time.perf_counter() - t0
+        out.append({"config": "8(f) rank 3: neibourhoods %s moves, radius %d, 1190 Miller-Schupp presentations" % (
+                        "classic" if classic else "prime", radius),
+                    "wall_s": dt, "total_states": int(sizes.sum()), "states_per_s": float(sizes.sum()) / dt,
+                    "min": int(sizes.min()), "max": int(sizes.max()), "checksum": int((sizes * np.arange(1, len(sizes) + 1)).sum()),
+                    "reference": "compiled neibourhoods.cpp: about 1.5 s per presentation and move set on one core"})
+    return out
+
+
 if __name__ == "__main__":
     dev = torch.device("cuda:0")
     which = sys.argv[1:] or ["greedy", "expand", "ppo"]
@@ -210,6 +250,12 @@ if __name__ == "__main__":
             print(json.dumps(cfg_ppo(dev)))
         elif w == "replay":
             print(json.dumps(cfg_replay(dev)))
+        elif w == "graph":
+            for line in cfg_graph(dev, int(os.environ.get("ACX_GRAPH_N", "14"))):
+                print(json.dumps(line))
+        elif w == "balls":
+            for line in cfg_balls(dev):
+                print(json.dumps(line))
         elif w == "bfs":
             import bench_bfs
             print(json.dumps(bench_bfs.run(dev)))

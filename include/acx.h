@@ -238,6 +238,58 @@ int acx_peer_export(const void* ptr, uint8_t* handle64);
 int acx_peer_open(const uint8_t* handle64, void** ptr);
 int acx_peer_close(void* ptr);
 
+/* ---- Graph engine: the reference's native C++ programs ---------------------------------
+ * barcode_analysis/simplex_data_generation/{classic,prime}_moves/ac_bfs.cpp:13-97 (BFS from (a, b) over UNORDERED
+ * relator pairs of total size <= n with full free reduction; node list, edge list and both filtrations) and
+ * barcode_analysis/5_steps_neibourhoods/neibourhoods.cpp:18-54 (size of the radius-r ball around a presentation).
+ * A node is 16*W bytes (W = width_words in {2, 4, 8}): sign / type planes of both relators, lengths and a 16-bit
+ * instance number in the spare top bytes; a relator holds at most 32*W - 8 letters.  Node ids are the reference's
+ * names (discovery order of its FIFO loop, ac_bfs.cpp:44-69). */
+typedef struct acx_graph_step {
+    int32_t width_words; /* W */
+    int32_t classic;     /* 1: the 14 classic moves, 0: the 12 prime moves (AC_UTILS_as_sets.h:298-363) */
+    int32_t max_total;   /* drop children with len(r1)+len(r2) > max_total (ac_bfs.cpp:59); <= 0: no limit */
+    int32_t want_edges;  /* emit the edge list of the step (ac_bfs.cpp:72-79) */
+    int32_t allow_empty; /* 1: a relator may cancel completely (neibourhoods.cpp keeps plain vectors); 0: that sets
+                            counts[2] (ac_bfs.cpp's Hash() cannot represent it, AC_UTILS_as_sets.h:118-139) */
+    uint32_t* nodes;     /* [capacity, 4W] node store in id order; capacity >= n_nodes + n_parents * n_moves */
+    int64_t n_nodes;     /* nodes committed before this step */
+    int64_t parent_first, n_parents; /* ids [parent_first, parent_first + n_parents) are expanded */
+    uint64_t* table;     /* open-addressing visited set, tcap slots (power of two, >= 2 * capacity in use) */
+    int64_t tcap;
+    /* scratch per candidate, C = n_parents * n_moves (14 or 12) */
+    uint32_t* cand;      /* [C, 4W] */
+    int64_t* cid;        /* [C] */
+    int64_t* slot;       /* [C] */
+    uint16_t* csize;     /* [C] */
+    uint8_t* flag;       /* [C] */
+    int64_t* excl;       /* [C] */
+    void* scan_tmp;      /* acx_graph_scan_bytes(C) bytes */
+    int64_t scan_tmp_bytes;
+    /* outputs */
+    uint16_t* node_size; /* [capacity] total length per node id (zero_filtrations) */
+    int64_t* edges;      /* [C, 2] (parent id, child id) of this step in the reference's emission order */
+    uint16_t* edge_filt; /* [C] max(size(parent), size(child)) (one_filtrations) */
+    int64_t* counts;     /* int64[4]: [0] new nodes, [1] edges of the step, [2] != 0: a relator overflowed the
+                            planes or cancelled completely (caller raises); caller zeroes [2] once */
+} acx_graph_step_t;
+
+int64_t acx_graph_scan_bytes(int64_t n_candidates);
+int acx_graph_step(const acx_graph_step_t* step, acx_stream_t stream);
+/* int8 rows [r1 | r2] (non-zero entries of each half, neibourhoods.cpp:74-86) -> sorted nodes (sort_,
+ * AC_UTILS_no_hash.cpp:120-136); inst may be NULL (0).  ok_out[j] = 0: letters outside {+-1,+-2}, not freely
+ * reduced, empty or too long for the planes. */
+int acx_graph_pack(const int8_t* rows, int64_t n, int m, const int32_t* inst, int width_words, uint32_t* nodes_out,
+                   uint8_t* ok_out, acx_stream_t stream);
+int acx_graph_unpack(const uint32_t* nodes, int64_t n, int width_words, int m, int8_t* rows_out, int32_t* inst_out,
+                     acx_stream_t stream);
+/* insert node ids [0, n_nodes) into a zeroed table (after growing it, or for the roots) */
+int acx_graph_rehash(const uint32_t* nodes, int64_t n_nodes, int width_words, uint64_t* table, int64_t tcap,
+                     acx_stream_t stream);
+/* counts[i] += number of nodes of instance i (ball sizes, neibourhoods.cpp:30-48) */
+int acx_graph_count_instances(const uint32_t* nodes, int64_t n_nodes, int width_words, int64_t* counts, int64_t n_inst,
+                              acx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -99,3 +99,78 @@ extern "C" int acxh_move_batch(const int8_t* in, const uint8_t* moves, int8_t* o
     else return -1;
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Graph engine (csrc/acx_graph.cuh) on the CPU: the same functors and the same graph_step<> template as
+// libacx.so, driven by a sequential executor.  Order-free functors run in a permuted order
+// (acxh_graph_set_order: 0 forward, 1 reverse, 2 strided permutation) so that the claim-replacement path
+// of the visited-set probe, which a forward sweep never takes, is exercised too.
+#include "../../ac-solver-caltech_b200/csrc/acx_graph.cuh"
+
+static int g_order = 0;
+
+struct HostExec {
+    template <class F>
+    void run(int64_t n, const F& f) {
+        for (int64_t i = 0; i < n; ++i) f(i);
+    }
+    template <class F>
+    void run_shuffled(int64_t n, const F& f) {
+        if (g_order == 0) {
+            for (int64_t i = 0; i < n; ++i) f(i);
+        } else if (g_order == 1) {
+            for (int64_t i = n - 1; i >= 0; --i) f(i);
+        } else {
+            if (n <= 0) return;
+            int64_t step = 7919;  // a prime that does not divide n: i -> (i * step) % n is a permutation
+            if (n % step == 0) step = 7927;
+            if (n % step == 0) step = 1;
+            for (int64_t i = 0; i < n; ++i) f((int64_t)(((__int128)i * step) % n));
+        }
+    }
+    int scan(const uint8_t* flag, int64_t* excl, int64_t n, void*, int64_t) {
+        int64_t run = 0;
+        for (int64_t i = 0; i < n; ++i) {
+            excl[i] = run;
+            run += flag[i];
+        }
+        return 0;
+    }
+};
+
+#define ACXH_DISPATCH(w, CALL)                          \
+    switch (w) {                                        \
+        case 2: { constexpr int W = 2; CALL; } break;   \
+        case 4: { constexpr int W = 4; CALL; } break;   \
+        case 8: { constexpr int W = 8; CALL; } break;   \
+        default: return -1;                             \
+    }
+
+extern "C" void acxh_graph_set_order(int order) { g_order = order; }
+extern "C" int64_t acxh_graph_scan_bytes(int64_t) { return 1; }
+extern "C" int acxh_graph_step(const acx_graph_step_t* a, void*) {
+    HostExec ex;
+    int rc = 0;
+    ACXH_DISPATCH(a->width_words, rc = (graph_step<W, HostExec>(ex, *a)));
+    return rc;
+}
+extern "C" int acxh_graph_pack(const int8_t* rows, int64_t n, int m, const int32_t* inst, int w, uint32_t* nodes, uint8_t* ok, void*) {
+    HostExec ex;
+    ACXH_DISPATCH(w, ex.run(n, GPackRows<W>{rows, m, inst, nodes, ok}));
+    return 0;
+}
+extern "C" int acxh_graph_unpack(const uint32_t* nodes, int64_t n, int w, int m, int8_t* rows, int32_t* inst, void*) {
+    HostExec ex;
+    ACXH_DISPATCH(w, ex.run(n, GUnpackRows<W>{nodes, m, rows, inst}));
+    return 0;
+}
+extern "C" int acxh_graph_rehash(const uint32_t* nodes, int64_t n, int w, uint64_t* table, int64_t tcap, void*) {
+    HostExec ex;
+    ACXH_DISPATCH(w, ex.run_shuffled(n, GRehash<W>{nodes, table, tcap}));
+    return 0;
+}
+extern "C" int acxh_graph_count_instances(const uint32_t* nodes, int64_t n, int w, int64_t* counts, int64_t n_inst, void*) {
+    HostExec ex;
+    ACXH_DISPATCH(w, ex.run(n, GCountInst<W>{nodes, counts, n_inst}));
+    return 0;
+}

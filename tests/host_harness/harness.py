@@ -16,7 +16,8 @@ _lib = None
 
 
 def build():
-    deps = glob.glob(os.path.join(ROOT, "ac-solver-caltech_b200", "csrc", "*.cuh")) + [os.path.join(HERE, "acx_host.cu")]
+    deps = glob.glob(os.path.join(ROOT, "ac-solver-caltech_b200", "csrc", "*.cuh")) + [os.path.join(HERE, "acx_host.cu"),
+                                                                                      os.path.join(ROOT, "include", "acx.h")]
     if os.path.exists(SO) and os.path.getmtime(SO) >= max(os.path.getmtime(d) for d in deps):
         return SO
     subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O2",
@@ -30,8 +31,39 @@ def lib():
         L = ctypes.CDLL(build())
         L.acxh_move_batch.argtypes = [_i8p, _u8p, _i8p, _u8p, _u8p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
                                       ctypes.c_int, ctypes.c_int]
+        _P, _I64, _I32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int
+        L.acxh_graph_set_order.argtypes = [_I32]
+        L.acxh_graph_set_order.restype = None
+        L.acxh_graph_scan_bytes.argtypes = [_I64]
+        L.acxh_graph_scan_bytes.restype = _I64
+        L.acxh_graph_step.argtypes = [_P, _P]
+        L.acxh_graph_pack.argtypes = [_P, _I64, _I32, _P, _I32, _P, _P, _P]
+        L.acxh_graph_unpack.argtypes = [_P, _I64, _I32, _I32, _P, _P, _P]
+        L.acxh_graph_rehash.argtypes = [_P, _I64, _I32, _P, _I64, _P]
+        L.acxh_graph_count_instances.argtypes = [_P, _I64, _I32, _P, _I64, _P]
         _lib = L
     return _lib
+
+
+class HostGraphBackend:
+    """Stand-in for acx.graph._CudaBackend in the CPU suite: the same csrc/acx_graph.cuh functors and
+    graph_step<> template, run sequentially on CPU tensors (order: 0 forward, 1 reverse, 2 permuted)."""
+
+    def __init__(self, order=0):
+        import torch
+
+        self.dev = torch.device("cpu")
+        self.stream = None
+        self.L = lib()
+        self.order = order
+
+    def call(self, name, *args):
+        self.L.acxh_graph_set_order(self.order)
+        rc = getattr(self.L, "acxh_graph_" + name)(*args, None)
+        assert rc == 0, (name, rc)
+
+    def scan_bytes(self, n):
+        return int(self.L.acxh_graph_scan_bytes(n))
 
 
 def move_batch(states, moves, cyclical, variant=0, inplace=1):
