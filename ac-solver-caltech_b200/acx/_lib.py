@@ -58,6 +58,7 @@ _SIGNATURES = {
     "acx_graph_unpack": (_I32, [_PTR, _I64, _I32, _I32, _PTR, _PTR, _PTR]),
     "acx_graph_rehash": (_I32, [_PTR, _I64, _I32, _PTR, _I64, _PTR]),
     "acx_graph_count_instances": (_I32, [_PTR, _I64, _I32, _PTR, _I64, _PTR]),
+    "acx_ms_enumerate": (_I32, [_I32, _I64, _I64, _PTR, _PTR, _PTR]),
 }
 
 

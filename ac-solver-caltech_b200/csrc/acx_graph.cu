@@ -7,6 +7,7 @@
 #include "../../include/acx.h"
 #include "acx_common.h"
 #include "acx_graph.cuh"
+#include "acx_ms.cuh"
 
 #include <cub/device/device_scan.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
@@ -156,6 +157,18 @@ extern "C" int acx_graph_count_instances(const uint32_t* nodes, int64_t n_nodes,
     GpuExec ex;
     if (int rc = make_exec(ex, stream)) return rc;
     ACX_GRAPH_DISPATCH(width_words, ex.run(n_nodes, GCountInst<W>{nodes, counts, n_inst}));
+    ACX_CUDA(ex.err);
+    return ACX_OK;
+}
+
+extern "C" int acx_ms_enumerate(int w_len, int64_t first, int64_t count, uint64_t* key_out, uint64_t* rel_out, acx_stream_t stream) {
+    if (w_len < 1 || w_len > 15 || first < 0 || count < 0 || first + count > (1ll << (2 * w_len)))
+        return acx_fail(ACX_ERR_ARG, "acx_ms_enumerate: need 1 <= w_len <= 15 and [first, first + count) inside [0, 4^w_len)");
+    if (count == 0) return ACX_OK;
+    if (!key_out || !rel_out) return acx_fail(ACX_ERR_ARG, "acx_ms_enumerate: null pointer");
+    GpuExec ex;
+    if (int rc = make_exec(ex, stream)) return rc;
+    ex.run(count, MsEnumerate{w_len, first, key_out, rel_out});
     ACX_CUDA(ex.err);
     return ACX_OK;
 }

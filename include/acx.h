@@ -290,6 +290,13 @@ int acx_graph_rehash(const uint32_t* nodes, int64_t n_nodes, int width_words, ui
 int acx_graph_count_instances(const uint32_t* nodes, int64_t n_nodes, int width_words, int64_t* counts, int64_t n_inst,
                               acx_stream_t stream);
 
+/* Enumeration step of generate_miller_schupp_presentations (ac_solver/search/miller_schupp/miller_schupp.py:20-83):
+ * for the words [first, first + count) of itertools.product([1, 2, -1, -2], repeat=w_len) (:53) apply the x-exponent
+ * filter (:56-57), reduce x^-1 w freely and cyclically (:60-63), drop x^-1 (:66-67).  rel_out = reduced relator, 2 bits
+ * per letter (0..3 = 1, 2, -1, -2) | length << 32; key_out = its minimum rotation | length << 32 (the class the
+ * `seen` set of :69-75 identifies), ~0 for a word that was filtered out.  1 <= w_len <= 15. */
+int acx_ms_enumerate(int w_len, int64_t first, int64_t count, uint64_t* key_out, uint64_t* rel_out, acx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

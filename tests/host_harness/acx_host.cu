@@ -174,3 +174,11 @@ extern "C" int acxh_graph_count_instances(const uint32_t* nodes, int64_t n, int 
     ACXH_DISPATCH(w, ex.run(n, GCountInst<W>{nodes, counts, n_inst}));
     return 0;
 }
+
+// Miller-Schupp enumeration functor (csrc/acx_ms.cuh) on the CPU
+#include "../../ac-solver-caltech_b200/csrc/acx_ms.cuh"
+extern "C" int acxh_ms_enumerate(int w_len, int64_t first, int64_t count, uint64_t* key, uint64_t* rel, void*) {
+    HostExec ex;
+    ex.run(count, MsEnumerate{w_len, first, key, rel});
+    return 0;
+}

@@ -41,6 +41,7 @@ def lib():
         L.acxh_graph_unpack.argtypes = [_P, _I64, _I32, _I32, _P, _P, _P]
         L.acxh_graph_rehash.argtypes = [_P, _I64, _I32, _P, _I64, _P]
         L.acxh_graph_count_instances.argtypes = [_P, _I64, _I32, _P, _I64, _P]
+        L.acxh_ms_enumerate.argtypes = [_I32, _I64, _I64, _P, _P, _P]
         _lib = L
     return _lib
 
@@ -78,3 +79,16 @@ def move_batch(states, moves, cyclical, variant=0, inplace=1):
                                variant, inplace)
     assert rc == 0
     return out, lens, st
+
+
+class HostMsBackend:
+    """Stand-in for the CUDA enumeration step of ac_solver.search.miller_schupp (csrc/acx_ms.cuh on the CPU)."""
+
+    def __init__(self):
+        import torch
+
+        self.dev = torch.device("cpu")
+        self.L = lib()
+
+    def enumerate(self, w_len, first, count, key, rel):
+        assert self.L.acxh_ms_enumerate(w_len, first, count, key.data_ptr(), rel.data_ptr(), None) == 0
