@@ -30,7 +30,7 @@ class _Step(ctypes.Structure):  # acx_graph_step_t (include/acx.h)
     _fields_ = [("width_words", ctypes.c_int32), ("classic", ctypes.c_int32), ("max_total", ctypes.c_int32),
                 ("want_edges", ctypes.c_int32), ("allow_empty", ctypes.c_int32), ("nodes", ctypes.c_void_p), ("n_nodes", ctypes.c_int64),
                 ("parent_first", ctypes.c_int64), ("n_parents", ctypes.c_int64), ("table", ctypes.c_void_p),
-                ("tcap", ctypes.c_int64), ("cand", ctypes.c_void_p), ("cid", ctypes.c_void_p), ("slot", ctypes.c_void_p),
+                ("tcap", ctypes.c_int64), ("cand", ctypes.c_void_p), ("ref", ctypes.c_void_p),
                 ("csize", ctypes.c_void_p), ("flag", ctypes.c_void_p), ("excl", ctypes.c_void_p),
                 ("scan_tmp", ctypes.c_void_p), ("scan_tmp_bytes", ctypes.c_int64), ("node_size", ctypes.c_void_p),
                 ("edges", ctypes.c_void_p), ("edge_filt", ctypes.c_void_p), ("counts", ctypes.c_void_p)]
@@ -81,8 +81,7 @@ class GraphEngine:
         d = self.be.dev
         C = self.chunk * self.nm
         self.cand = torch.empty((C, 4 * self.W), dtype=torch.int32, device=d)
-        self.cid = torch.empty((C,), dtype=torch.int64, device=d)
-        self.slot = torch.empty((C,), dtype=torch.int64, device=d)
+        self.ref = torch.empty((C,), dtype=torch.int64, device=d)
         self.csize = torch.empty((C,), dtype=torch.int16, device=d)
         self.flag = torch.empty((C,), dtype=torch.uint8, device=d)
         self.excl = torch.empty((C,), dtype=torch.int64, device=d)
@@ -142,8 +141,8 @@ class GraphEngine:
         self._reserve(C)
         s = _Step(self.W, int(self.classic), self.max_total, int(self.want_edges), int(self.allow_empty),
                   self.nodes.data_ptr(), self.n_nodes,
-                  first, n_parents, self.table.data_ptr(), self.tcap, self.cand.data_ptr(), self.cid.data_ptr(),
-                  self.slot.data_ptr(), self.csize.data_ptr(), self.flag.data_ptr(), self.excl.data_ptr(),
+                  first, n_parents, self.table.data_ptr(), self.tcap, self.cand.data_ptr(), self.ref.data_ptr(),
+                  self.csize.data_ptr(), self.flag.data_ptr(), self.excl.data_ptr(),
                   self.scan_tmp.data_ptr(), self.scan_tmp.numel(), self.node_size.data_ptr(), self.edges.data_ptr(),
                   self.edge_filt.data_ptr(), self.counts.data_ptr())
         self.be.call("step", ctypes.byref(s))
@@ -173,8 +172,8 @@ class GraphEngine:
 
 
 def ac_graph_bfs(n_max, moves="classic", chunk=1 << 18, width_words=2, device="cuda:0", with_rows=False, _backend=None):
-    """ac_bfs.cpp main(): returns dict(sizes int16[N] (zero_filtrations), edges int64[E,2] (one_simplices),
-    efilt int16[E] (one_filtrations), levels=[frontier sizes], rows=int8[N, 2(n_max-1)] if with_rows)."""
+    """ac_bfs.cpp main(): returns dict(sizes int16[N] (zero_filtrations), edges int32[E,2] (one_simplices; int64 beyond
+    2^31 nodes), efilt uint8[E] (one_filtrations), levels=[frontier sizes], rows=int8[N, 2(n_max-1)] if with_rows)."""
     if moves not in ("classic", "prime"):
         raise ValueError("moves must be 'classic' or 'prime'")
     n_max = int(n_max)
@@ -188,14 +187,30 @@ def ac_graph_bfs(n_max, moves="classic", chunk=1 << 18, width_words=2, device="c
         levels.append(hi - lo)
         eng.expand_level(lo, hi)
         lo, hi = hi, eng.n_nodes
-    d = eng.be.dev
-    edges = torch.cat(eng.edge_parts) if eng.edge_parts else torch.empty((0, 2), dtype=torch.int64, device=d)
-    efilt = torch.cat(eng.filt_parts) if eng.filt_parts else torch.empty((0,), dtype=torch.int16, device=d)
-    out = dict(sizes=eng.node_size[: eng.n_nodes].cpu().numpy(), edges=edges.cpu().numpy(), efilt=efilt.cpu().numpy(),
-               levels=levels)
+    edges, efilt = _gather_edges(eng)
+    out = dict(sizes=eng.node_size[: eng.n_nodes].cpu().numpy(), edges=edges, efilt=efilt, levels=levels)
     if with_rows:
         out["rows"] = eng.rows(max(n_max - 1, 1))[0]
     return out
+
+
+def _gather_edges(eng):
+    """Edge list and filtration of all steps on the host: int32 pairs while the names fit (int64 beyond 2^31 nodes) and
+    uint8 sizes, copied straight from the per-step device buffers into pinned memory."""
+    E = eng.n_edges
+    cuda = eng.be.dev.type == "cuda"
+    idt = torch.int32 if eng.n_nodes < (1 << 31) else torch.int64
+    edges = torch.empty((E, 2), dtype=idt, pin_memory=cuda)
+    efilt = torch.empty((E,), dtype=torch.uint8, pin_memory=cuda)
+    pos = 0
+    for e, f in zip(eng.edge_parts, eng.filt_parts):
+        k = e.shape[0]
+        edges[pos:pos + k].copy_(e.to(idt), non_blocking=True)
+        efilt[pos:pos + k].copy_(f.to(torch.uint8), non_blocking=True)
+        pos += k
+    if cuda:
+        torch.cuda.current_stream(eng.be.dev).synchronize()
+    return edges.numpy(), efilt.numpy()
 
 
 def _join(fmt, arr):

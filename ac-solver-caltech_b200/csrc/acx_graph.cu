@@ -98,7 +98,7 @@ extern "C" int acx_graph_step(const acx_graph_step_t* step, acx_stream_t stream)
         return acx_fail(ACX_ERR_ARG, "acx_graph_step: table capacity must be a power of two >= 2 * (n_nodes + candidates)");
     if (a.n_nodes + C > (int64_t)G_VAL) return acx_fail(ACX_ERR_ARG, "acx_graph_step: node ids are 47 bits");
     if (C == 0) return ACX_OK;
-    if (!a.nodes || !a.table || !a.cand || !a.cid || !a.slot || !a.csize || !a.flag || !a.excl || !a.scan_tmp || !a.node_size || !a.counts)
+    if (!a.nodes || !a.table || !a.cand || !a.ref || !a.csize || !a.flag || !a.excl || !a.scan_tmp || !a.node_size || !a.counts)
         return acx_fail(ACX_ERR_ARG, "acx_graph_step: null pointer");
     if (a.want_edges && (!a.edges || !a.edge_filt)) return acx_fail(ACX_ERR_ARG, "acx_graph_step: want_edges needs edges / edge_filt");
     if (((uintptr_t)a.nodes | (uintptr_t)a.cand) & 15u) return acx_fail(ACX_ERR_ARG, "acx_graph_step: nodes / cand must be 16-byte aligned");

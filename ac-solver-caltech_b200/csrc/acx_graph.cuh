@@ -324,15 +324,24 @@ struct GCountInst {
 
 // candidate c = (parent - parent_first) * n_moves + move: the position at which the reference's FIFO loop
 // reaches the child (ac_bfs.cpp:52-57), so "lowest c wins" reproduces its discovery order.
+// Work item i of the expand pass is laid out so that the 32 lanes of a warp apply the SAME move to 32 consecutive
+// parents (no divergence between the concat / conjugate / inverse paths, coalesced parent loads):
+//   i = (group * n_moves + move) * 32 + lane,  parent = group * 32 + lane.
+static constexpr uint64_t G_FOUND = 1ull << 62;  // ref[c] = G_FOUND | node id: the child is a committed node
+
 template <int W>
 struct GExpand {
     acx_graph_step_t a;
     int nm;
-    ACX_HD void operator()(int64_t c) const {
-        const int64_t par = a.parent_first + c / nm;
-        const int k = (int)(c % nm);
+    ACX_HD void operator()(int64_t i) const {
+        const int lane = (int)(i & 31);
+        const int64_t gk = i >> 5;
+        const int k = (int)(gk % nm);
+        const int64_t local = (gk / nm) * 32 + lane;
+        if (local >= a.n_parents) return;
+        const int64_t c = local * nm + k;
         const int cap = 32 * W - 8;
-        const GPres<W> p = g_unpack<W>(g_load<W>(a.nodes, par));
+        const GPres<W> p = g_unpack<W>(g_load<W>(a.nodes, a.parent_first + local));
         GPres<W> ch;
         const int st = g_move<W>(p, k, a.classic != 0, cap, a.allow_empty != 0, ch);
         bool skip = false, err = false;
@@ -351,8 +360,7 @@ struct GExpand {
             a.counts[2] = 1;
             skip = true;
         }
-        a.cid[c] = -1;
-        a.slot[c] = -1;
+        a.ref[c] = -1;
         a.csize[c] = skip ? (uint16_t)0 : (uint16_t)total;
         if (!skip) g_store<W>(a.cand, c, g_pack<W>(ch));
     }
@@ -374,7 +382,7 @@ struct GProbe {
             if (e == 0ull) {
                 e = g_cas(a.table + slot, 0ull, mine);
                 if (e == 0ull) {
-                    a.slot[c] = (int64_t)slot;
+                    a.ref[c] = (int64_t)slot;
                     return;
                 }
             }
@@ -383,13 +391,13 @@ struct GProbe {
                     // a claim is only ever replaced by a claim of an equal state, so one comparison settles it
                     if (g_equal<W>(s, g_load<W>(a.cand, (int64_t)(e & G_VAL)))) {
                         g_min(a.table + slot, mine);
-                        a.slot[c] = (int64_t)slot;
+                        a.ref[c] = (int64_t)slot;
                         return;
                     }
                 } else {
                     const int64_t id = (int64_t)(e & G_VAL);
                     if (g_equal<W>(s, g_load<W>(a.nodes, id))) {
-                        a.cid[c] = id;
+                        a.ref[c] = (int64_t)(G_FOUND | (uint64_t)id);
                         return;
                     }
                 }
@@ -403,25 +411,12 @@ template <int W>
 struct GResolve {  // flag = this candidate is the first discovery of a new state
     acx_graph_step_t a;
     ACX_HD void operator()(int64_t c) const {
-        const int64_t s = a.slot[c];
-        a.flag[c] = (s >= 0 && (a.table[s] & (G_PROV | G_VAL)) == (G_PROV | (uint64_t)c)) ? 1 : 0;
+        const int64_t s = a.ref[c];
+        a.flag[c] = (s >= 0 && !((uint64_t)s & G_FOUND) && (a.table[s] & (G_PROV | G_VAL)) == (G_PROV | (uint64_t)c)) ? 1 : 0;
     }
 };
 
-template <int W>
-struct GCommit {  // winners become nodes, in candidate order (ac_bfs.cpp:60-69)
-    acx_graph_step_t a;
-    ACX_HD void operator()(int64_t c) const {
-        if (!a.flag[c]) return;
-        const int64_t id = a.n_nodes + a.excl[c];
-        g_store<W>(a.nodes, id, g_load<W>(a.cand, c));
-        a.node_size[id] = a.csize[c];
-        const int64_t s = a.slot[c];
-        a.table[s] = (a.table[s] & G_TAG) | (uint64_t)id;
-    }
-};
-
-struct GTotal {  // counts[which] = number of flagged candidates
+struct GTotal {  // out[0] = number of flagged candidates
     const uint8_t* flag;
     const int64_t* excl;
     int64_t n;
@@ -429,21 +424,36 @@ struct GTotal {  // counts[which] = number of flagged candidates
     ACX_HD void operator()(int64_t) const { out[0] = excl[n - 1] + (int64_t)flag[n - 1]; }
 };
 
+// Winners become nodes in candidate order (ac_bfs.cpp:60-69: id = n_nodes + exclusive count of winners before c);
+// in the same pass every in-range child learns its name and flags its edge (ac_bfs.cpp:72-79: an edge whenever the
+// child's name is larger than the parent's).  A loser may read the slot before or after the winner has replaced the
+// claim by the node id: both forms name the same node (claim -> n_nodes + excl[winner]).
 template <int W>
-struct GEdgeFlag {  // ac_bfs.cpp:72-79: an edge for every in-range child whose name is larger than the parent's
+struct GCommitEdge {
     acx_graph_step_t a;
     int nm;
     ACX_HD void operator()(int64_t c) const {
+        const bool win = a.flag[c] != 0;
+        if (!win && !a.want_edges) return;
         uint8_t f = 0;
         if (a.csize[c] != 0) {
-            int64_t cc = a.cid[c];
-            if (cc < 0) {
-                cc = (int64_t)(a.table[a.slot[c]] & G_VAL);  // committed by now: the winner's node id
-                a.cid[c] = cc;
+            const int64_t r = a.ref[c];
+            int64_t cc;
+            if (win) {
+                cc = a.n_nodes + a.excl[c];
+                g_store<W>(a.nodes, cc, g_load<W>(a.cand, c));
+                a.node_size[cc] = a.csize[c];
+                a.table[r] = (g_ld(a.table + r) & G_TAG) | (uint64_t)cc;
+            } else if ((uint64_t)r & G_FOUND) {
+                cc = (int64_t)((uint64_t)r & G_VAL);
+            } else {
+                const uint64_t e = g_ld(a.table + r);
+                cc = (e & G_PROV) ? a.n_nodes + a.excl[(int64_t)(e & G_VAL)] : (int64_t)(e & G_VAL);
             }
+            a.ref[c] = cc;
             f = (a.parent_first + c / nm) < cc ? 1 : 0;
         }
-        a.flag[c] = f;
+        if (a.want_edges) a.flag[c] = f;
     }
 };
 
@@ -455,7 +465,7 @@ struct GEdgeWrite {
         if (!a.flag[c]) return;
         const int64_t pos = a.excl[c], par = a.parent_first + c / nm;
         a.edges[2 * pos] = par;
-        a.edges[2 * pos + 1] = a.cid[c];
+        a.edges[2 * pos + 1] = a.ref[c];
         const uint16_t ps = a.node_size[par], cs = a.csize[c];
         a.edge_filt[pos] = ps > cs ? ps : cs;  // ac_bfs.cpp:76
     }
@@ -470,14 +480,13 @@ int graph_step(Exec& ex, const acx_graph_step_t& a) {
     const int nm = a.classic ? 14 : 12;
     const int64_t C = a.n_parents * nm;
     if (C == 0) return 0;
-    ex.run_shuffled(C, GExpand<W>{a, nm});
+    ex.run_shuffled(((a.n_parents + 31) / 32) * 32 * nm, GExpand<W>{a, nm});
     ex.run_shuffled(C, GProbe<W>{a});
     ex.run_shuffled(C, GResolve<W>{a});
     if (int rc = ex.scan(a.flag, a.excl, C, a.scan_tmp, a.scan_tmp_bytes)) return rc;
     ex.run(1, GTotal{a.flag, a.excl, C, a.counts});
-    ex.run_shuffled(C, GCommit<W>{a});
+    ex.run_shuffled(C, GCommitEdge<W>{a, nm});
     if (a.want_edges) {
-        ex.run_shuffled(C, GEdgeFlag<W>{a, nm});
         if (int rc = ex.scan(a.flag, a.excl, C, a.scan_tmp, a.scan_tmp_bytes)) return rc;
         ex.run(1, GTotal{a.flag, a.excl, C, a.counts + 1});
         ex.run_shuffled(C, GEdgeWrite<W>{a, nm});

@@ -259,8 +259,7 @@ typedef struct acx_graph_step {
     int64_t tcap;
     /* scratch per candidate, C = n_parents * n_moves (14 or 12) */
     uint32_t* cand;      /* [C, 4W] */
-    int64_t* cid;        /* [C] */
-    int64_t* slot;       /* [C] */
+    int64_t* ref;        /* [C] claimed table slot / committed node id of every candidate */
     uint16_t* csize;     /* [C] */
     uint8_t* flag;       /* [C] */
     int64_t* excl;       /* [C] */
