@@ -311,3 +311,45 @@ def read_do_and_write(sourcefile, outfile, r, classic, verbose=True, **kw):
                 print("(%s, %s)" % ("".join(_LETTER[v] for v in a), "".join(_LETTER[v] for v in b)))
             f.write("%d\n" % int(s))
     return 0
+
+
+def _main(argv=None):
+    """Command lines of the two reference programs (`a.out n`; `a.out` in a directory with the two .txt files)."""
+    import argparse
+    import time
+
+    ap = argparse.ArgumentParser(prog="python -m acx.graph")
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    a = sub.add_parser("ac_bfs", help="simplex_data_generation/*/ac_bfs.cpp")
+    a.add_argument("n", type=int)
+    a.add_argument("--moves", choices=("classic", "prime"), default="classic")
+    a.add_argument("--outdir", default=".")
+    a.add_argument("--device", default="cuda:0")
+    b = sub.add_parser("neighbourhoods", help="5_steps_neibourhoods/neibourhoods.cpp")
+    b.add_argument("sourcefile", nargs="?")
+    b.add_argument("outfile", nargs="?")
+    b.add_argument("--radius", type=int, default=5)
+    b.add_argument("--moves", choices=("classic", "prime"), default="prime")
+    b.add_argument("--device", default="cuda:0")
+    args = ap.parse_args(argv)
+    if args.cmd == "ac_bfs":
+        print(args.n)  # ac_bfs.cpp:16
+        t0 = time.perf_counter()
+        write_simplex_files(ac_graph_bfs(args.n, args.moves, device=args.device), args.n, args.outdir)
+        print("time %d" % int((time.perf_counter() - t0) * 1e6))  # :95 (microseconds)
+        return 0
+    if args.sourcefile:
+        if not args.outfile:
+            ap.error("neighbourhoods: give both sourcefile and outfile, or neither")
+        return read_do_and_write(args.sourcefile, args.outfile, args.radius, args.moves == "classic", device=args.device)
+    # neibourhoods.cpp main() (:101-124): both files, classic first, then prime
+    solved, unsolved = "solved_miller_schupp_presentations.txt", "unsolved_miller_schupp_presentations.txt"
+    read_do_and_write(solved, "solved_clasic_moves", args.radius, True, device=args.device)
+    read_do_and_write(unsolved, "unsolved_clasic_moves", args.radius, True, device=args.device)
+    read_do_and_write(solved, "solved_prime_moves", args.radius, False, device=args.device)
+    read_do_and_write(unsolved, "unsolved_prime_moves", args.radius, False, device=args.device)
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(_main())
