@@ -45,6 +45,7 @@ _SIGNATURES = {
     "acx_bfs_window_partition": (_I32, [_PTR, _I64, _I64, _I64, _I64, _PTR, _PTR, _PTR, _I64, _PTR, _PTR, _I32, _PTR]),
     "acx_path_replay": (_I32, [_PTR, _PTR, _PTR, _I64, _I32, _I32, _I32, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR]),
     "acx_rows_features": (_I32, [_PTR, _I64, _I32, _PTR, _PTR]),
+    "acx_path_expand_cyclic": (_I32, [_PTR, _PTR, _PTR, _I64, _I32, _I32, _PTR, _PTR, _I32, _PTR, _PTR, _PTR, _PTR]),
     "acx_peer_alloc": (_I32, [_I64, _PTR]),
     "acx_peer_free": (_I32, [_PTR]),
     "acx_peer_export": (_I32, [_PTR, _PTR]),

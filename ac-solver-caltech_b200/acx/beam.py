@@ -8,8 +8,9 @@ back to torch for scoring.  Here one step is
     acx_rows_features / token ids on the device -> the caller's torch model -> stable top-k
 
 with the visited set, the node store and the scores resident in HBM.  Same signature and return value as the
-reference (`solved, path, stats`); `solution_cache` (a Python dict probed with rotation variants, :457-461,
-:500-509) is host-side memoisation and is not supported here.
+reference (`solved, path, stats`).  `solution_cache` (a Python dict probed with rotation variants, :457-461,
+:500-509) is honoured: the children of a step are looked up on the host in the reference's order, between the
+trivial test and the visited test (acx.solution_cache).
 """
 import time
 
@@ -19,6 +20,7 @@ import torch
 from . import _lib
 from .batch import _prep, _ptr
 from .bfs import U64_MAX, _next_pow2
+from .solution_cache import _check_cache_with_rotations
 
 
 def features(rows):
@@ -53,13 +55,15 @@ def beam_search(presentation, model, architecture="mlp", feat_mean=None, feat_st
                 solution_cache=None, time_limit=None):
     """Returns (solved, path, stats): path = [(action, total_length), ...] without a root sentinel (:89-96),
     stats = {'nodes_explored', 'steps'} (:496-497, :560)."""
-    if solution_cache is not None:
-        raise NotImplementedError("solution_cache is host-side memoisation of the reference driver; not part of the GPU path")
     root = np.ascontiguousarray(np.asarray(presentation), dtype=np.int8)
     rowb = len(root)
     m = rowb // 2
     if rowb % 4:
         raise ValueError("beam_search on the GPU needs an even max_relator_length")
+    if solution_cache is not None:  # :459-465
+        cached = _check_cache_with_rotations(tuple(int(v) for v in root), m, solution_cache)
+        if cached is not None:
+            return True, cached, {"nodes_explored": 1, "steps": 0, "cache_hit": True}
     dev = torch.device(device)
     stream = _prep(dev)
     L = _lib.lib()
@@ -77,13 +81,13 @@ def beam_search(presentation, model, architecture="mlp", feat_mean=None, feat_st
     total[0] = int(np.count_nonzero(root))
     _lib.check(L.acx_bfs_seed(_ptr(nodes), m, _ptr(table), tcap, 0, stream), "acx_bfs_seed")
 
-    def path_to(node, last_action):
+    def path_to(node, last_action, last_total=2):
         chain = []
         while node > 0:
             chain.append((int(action[node]), int(total[node])))
             node = int(parent[node])
         chain.reverse()
-        return chain + [(int(last_action), 2)]
+        return chain + [(int(last_action), int(last_total))]
 
     beam = torch.zeros((1,), dtype=torch.int64, device=dev)
     total_nodes, step = 1, 0
@@ -112,6 +116,18 @@ def beam_search(presentation, model, architecture="mlp", feat_mean=None, feat_st
         c_s, c_e, n_new = int(head[0]) & U64_MAX, int(head[1]) & U64_MAX, int(head[2])
         c_b = int(head[3]) if n_new >= need else U64_MAX
         first = min(c_s, c_e, c_b)
+        if solution_cache is not None:
+            # the cache is consulted per child between the trivial test and the visited test (:489-498): a hit at child c
+            # counts when no earlier child solved / raised and the budget was not reached before c
+            bound = min(n, c_s, c_e, c_b + 1 if c_b != U64_MAX else n)
+            rows_h = ch[:bound].cpu().numpy()
+            tots_h = ln[:bound].to(torch.int64).sum(dim=1).cpu().numpy()
+            for c in range(bound):
+                cached = _check_cache_with_rotations(tuple(rows_h[c].tolist()), m, solution_cache)
+                if cached is not None:
+                    before = int(cum[c - 1]) if c > 0 else 0
+                    path = path_to(int(beam[c // 12]), c % 12, int(tots_h[c])) + list(cached)
+                    return True, path, {"nodes_explored": total_nodes + before, "steps": step, "cache_hit": True}
         if first != U64_MAX and first == c_e:
             raise AssertionError("a relator became empty during the search: not a valid presentation")
         if first != U64_MAX and first == c_s:
@@ -156,8 +172,6 @@ def value_guided_greedy_search(presentation, model=None, architecture="mlp", fea
     Returns (solved, path, {'nodes_explored', 'min_length'})."""
     import heapq
 
-    if solution_cache is not None:
-        raise NotImplementedError("solution_cache is host-side memoisation of the reference driver; not part of the GPU path")
     root = np.ascontiguousarray(np.asarray(presentation), dtype=np.int8)
     rowb = len(root)
     m = rowb // 2
@@ -197,6 +211,10 @@ def value_guided_greedy_search(presentation, model=None, architecture="mlp", fea
         return path
 
     init_priority = float(total0) if use_length_priority else score(nodes[0:1])[0]
+    if solution_cache is not None:  # :325-330
+        cached = _check_cache_with_rotations(tuple(int(v) for v in root), m, solution_cache)
+        if cached is not None:
+            return True, cached, {"nodes_explored": 1, "min_length": 2, "cache_hit": True}
     heap = [(init_priority, 0, 0)]
     next_id, n_states, min_length = 1, 1, total0
     ch = torch.empty((12, rowb), dtype=torch.int8, device=dev)
@@ -218,6 +236,7 @@ def value_guided_greedy_search(presentation, model=None, architecture="mlp", fea
                                    mins[0:].data_ptr(), mins[1:].data_ptr(), 0, _ptr(is_new), stream), "acx_bfs_probe")
         h = torch.cat([ln.to(torch.int64).sum(dim=1), st.to(torch.int64), slot, is_new.to(torch.int64)]).tolist()
         tot, stat, slots, news = h[0:12], h[12:24], h[24:36], h[36:48]
+        ch_host = ch.cpu().numpy() if solution_cache is not None else None
         kids = []
         for a in range(12):
             if stat[a]:
@@ -228,6 +247,11 @@ def value_guided_greedy_search(presentation, model=None, architecture="mlp", fea
                     print(f"New min length: {min_length} (nodes: {n_states})")
             if tot[a] == 2:
                 return True, path_to(cur) + [(a, 2)], {"nodes_explored": n_states, "min_length": min_length}
+            if solution_cache is not None:  # :365-373
+                cached = _check_cache_with_rotations(tuple(ch_host[a].tolist()), m, solution_cache)
+                if cached is not None:
+                    return True, path_to(cur) + [(a, tot[a])] + list(cached), {"nodes_explored": n_states, "min_length": 2,
+                                                                              "cache_hit": True}
             if slots[a] >= 0:
                 kids.append(a)
         if kids:

@@ -13,6 +13,7 @@
 #include "../../include/acx.h"
 #include "acx_common.h"
 #include "acx_rows.cuh"
+#include "acx_cyclic_expand.cuh"
 
 namespace acx {
 
@@ -115,6 +116,39 @@ static int launch_replay(const int8_t* roots, const uint8_t* actions, const int3
     return ACX_OK;
 }
 
+// expand_path_with_cyclic_reductions for a batch of paths: one thread per path, row in shared memory.
+template <int W, int MS, int TR>
+__global__ void __launch_bounds__(TR) k_path_expand_cyclic(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t P,
+                                                           int T, int m, uint8_t* out_actions, uint16_t* out_totals, int cap,
+                                                           int32_t* out_len, int32_t* fail_step, uint8_t* status) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int rowb = 2 * m, pitch = (rowb + 7) / 8 * 8;
+    const int64_t p = (int64_t)blockIdx.x * TR + threadIdx.x;
+    if (p >= P) return;
+    uint8_t* row = smem + (size_t)threadIdx.x * pitch;
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(roots) + p * rowb;
+    for (int k = 0; k < rowb; ++k) row[k] = src[k];
+    const int n = min(path_len ? path_len[p] : T, T);
+    uint32_t st;
+    int fail;
+    const int o = expand_cyclic_path<W, MS>(row, m, actions + p * T, n, out_actions + p * cap, out_totals + p * cap, cap, st, fail);
+    out_len[p] = o;
+    fail_step[p] = fail;
+    status[p] = (uint8_t)st;
+}
+
+template <int W, int MS>
+static int launch_expand_cyclic(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t P, int T, int m,
+                                uint8_t* out_actions, uint16_t* out_totals, int cap, int32_t* out_len, int32_t* fail_step,
+                                uint8_t* status, cudaStream_t st) {
+    constexpr int TR = 64;
+    const size_t smem = (size_t)TR * ((2 * m + 7) / 8 * 8);
+    k_path_expand_cyclic<W, MS, TR><<<(unsigned)((P + TR - 1) / TR), TR, smem, st>>>(roots, actions, path_len, P, T, m, out_actions,
+                                                                                     out_totals, cap, out_len, fail_step, status);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
 // The 14 handcrafted features of value_search/feature_extraction.py:11-91, one thread per row, float32 out.
 // Counts run over the first len(r) letters of each relator (:50-61); the two ratios are computed in double and
 // rounded once to float32, as numpy does when it builds the float32 array from Python floats (:68-91).
@@ -174,4 +208,18 @@ extern "C" int acx_path_replay(const int8_t* roots, const uint8_t* actions, cons
     if (m <= 32) return launch_replay<1, 0, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
     if (m <= 64) return launch_replay<2, 0, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
     return launch_replay<4, 0, 64>(roots, actions, path_len, n_paths, max_steps, m, cyclical, states_out, lens_out, final_out, final_lens, fail_step, status, st);
+}
+
+extern "C" int acx_path_expand_cyclic(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t n_paths,
+                                      int max_steps, int m, uint8_t* out_actions, uint16_t* out_totals, int out_cap, int32_t* out_len,
+                                      int32_t* fail_step, uint8_t* status, acx_stream_t stream) {
+    if (n_paths < 0 || max_steps < 0 || out_cap < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH)
+        return acx_fail(ACX_ERR_ARG, "acx_path_expand_cyclic: need n_paths >= 0, max_steps >= 0, out_cap >= 0, 1 <= m <= 128");
+    if (n_paths == 0) return ACX_OK;
+    if (!roots || (max_steps > 0 && !actions) || (out_cap > 0 && (!out_actions || !out_totals)) || !out_len || !fail_step || !status)
+        return acx_fail(ACX_ERR_ARG, "acx_path_expand_cyclic: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (m <= 32) return launch_expand_cyclic<1, 0>(roots, actions, path_len, n_paths, max_steps, m, out_actions, out_totals, out_cap, out_len, fail_step, status, st);
+    if (m <= 64) return launch_expand_cyclic<2, 0>(roots, actions, path_len, n_paths, max_steps, m, out_actions, out_totals, out_cap, out_len, fail_step, status, st);
+    return launch_expand_cyclic<4, 0>(roots, actions, path_len, n_paths, max_steps, m, out_actions, out_totals, out_cap, out_len, fail_step, status, st);
 }

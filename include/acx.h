@@ -226,6 +226,15 @@ int acx_path_replay(const int8_t* roots, const uint8_t* actions, const int32_t* 
                     int cyclical, int8_t* states_out, uint8_t* lens_out, int8_t* final_out, uint8_t* final_lens,
                     int32_t* fail_step, uint8_t* status, acx_stream_t stream);
 
+/* expand_path_with_cyclic_reductions (value_search/value_guided_search.py:581-635) for a batch of compact paths found with
+ * cyclical=True: replay with free reduction only and insert the conjugation moves (:563-578) that perform the cyclic
+ * reductions.  out_actions uint8 / out_totals uint16 [n_paths, out_cap] receive the expanded (action, total_length) pairs,
+ * out_len[p] their number.  status: ACX_ROW_STATUS_*, or 3 = out_cap too small (retry with more room); fail_step as in
+ * acx_path_replay. */
+int acx_path_expand_cyclic(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t n_paths, int max_steps,
+                           int m, uint8_t* out_actions, uint16_t* out_totals, int out_cap, int32_t* out_len, int32_t* fail_step,
+                           uint8_t* status, acx_stream_t stream);
+
 /* The 14 handcrafted value-network features of value_search/feature_extraction.py:11-91, float32 [n, 14], computed
  * where the rows already are (removes the numpy hop of value_guided_search.py:49-63). */
 int acx_rows_features(const int8_t* rows, int64_t n, int m, float* features_out, acx_stream_t stream);

@@ -182,3 +182,26 @@ extern "C" int acxh_ms_enumerate(int w_len, int64_t first, int64_t count, uint64
     ex.run(count, MsEnumerate{w_len, first, key, rel});
     return 0;
 }
+
+// expand_path_with_cyclic_reductions (csrc/acx_cyclic_expand.cuh) on the CPU, one path per call of the HD function
+#include "../../ac-solver-caltech_b200/csrc/acx_cyclic_expand.cuh"
+extern "C" int acxh_path_expand_cyclic(const int8_t* roots, const uint8_t* actions, const int32_t* path_len, int64_t P, int T, int m,
+                                       uint8_t* out_actions, uint16_t* out_totals, int cap, int32_t* out_len, int32_t* fail_step,
+                                       uint8_t* status, void*) {
+    std::vector<uint64_t> scratch(2 * m / 8 + 2);
+    for (int64_t p = 0; p < P; ++p) {
+        uint8_t* row = reinterpret_cast<uint8_t*>(scratch.data());
+        memcpy(row, roots + p * 2 * m, 2 * m);
+        const int n = std::min(path_len ? path_len[p] : T, T);
+        uint32_t st;
+        int fail;
+        int o;
+        if (m <= 32) o = expand_cyclic_path<1, 0>(row, m, actions + p * T, n, out_actions + p * cap, out_totals + p * cap, cap, st, fail);
+        else if (m <= 64) o = expand_cyclic_path<2, 0>(row, m, actions + p * T, n, out_actions + p * cap, out_totals + p * cap, cap, st, fail);
+        else o = expand_cyclic_path<4, 0>(row, m, actions + p * T, n, out_actions + p * cap, out_totals + p * cap, cap, st, fail);
+        out_len[p] = o;
+        fail_step[p] = fail;
+        status[p] = (uint8_t)st;
+    }
+    return 0;
+}

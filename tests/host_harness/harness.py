@@ -42,6 +42,7 @@ def lib():
         L.acxh_graph_rehash.argtypes = [_P, _I64, _I32, _P, _I64, _P]
         L.acxh_graph_count_instances.argtypes = [_P, _I64, _I32, _P, _I64, _P]
         L.acxh_ms_enumerate.argtypes = [_I32, _I64, _I64, _P, _P, _P]
+        L.acxh_path_expand_cyclic.argtypes = [_P, _P, _P, _I64, _I32, _I32, _P, _P, _I32, _P, _P, _P, _P]
         _lib = L
     return _lib
 
@@ -92,3 +93,16 @@ class HostMsBackend:
 
     def enumerate(self, w_len, first, count, key, rel):
         assert self.L.acxh_ms_enumerate(w_len, first, count, key.data_ptr(), rel.data_ptr(), None) == 0
+
+
+class HostExpandBackend:
+    """Stand-in for acx.solution_cache._CudaExpand (csrc/acx_cyclic_expand.cuh on the CPU)."""
+
+    def __init__(self):
+        import torch
+
+        self.dev = torch.device("cpu")
+        self.L = lib()
+
+    def expand(self, *args):
+        assert self.L.acxh_path_expand_cyclic(*args, None) == 0

@@ -38,9 +38,15 @@ def _score(states, model, arch, mean, std, dev, dim):
         return torch.expm1(model(t).squeeze(-1)).cpu().numpy().tolist()
 
 
-def _beam_oracle(oracle, presentation, model, arch, mean, std, width, budget, dev, cyc):
+def _beam_oracle(oracle, presentation, model, arch, mean, std, width, budget, dev, cyc, cache=None):
+    from acx.solution_cache import _check_cache_with_rotations  # pinned by reference vectors (test_solution_cache.py)
+
     presentation = np.array(presentation, dtype=np.int8)
     m = len(presentation) // 2
+    if cache is not None:
+        hit = _check_cache_with_rotations(tuple(presentation.tolist()), m, cache)
+        if hit is not None:
+            return True, hit, {"nodes_explored": 1, "steps": 0, "cache_hit": True}
     l1, l2 = int(np.count_nonzero(presentation[:m])), int(np.count_nonzero(presentation[m:]))
     parent_map = {0: (None, l1 + l2, None)}
     next_id = 1
@@ -69,6 +75,11 @@ def _beam_oracle(oracle, presentation, model, arch, mean, std, width, budget, de
                 tup = tuple(ns)
                 if new_length == 2:
                     return True, recon(pid) + [(action, new_length)], {"nodes_explored": total_nodes, "steps": step}
+                if cache is not None:
+                    hit = _check_cache_with_rotations(tuple(int(v) for v in ns), m, cache)
+                    if hit is not None:
+                        return True, recon(pid) + [(action, new_length)] + list(hit), {"nodes_explored": total_nodes, "steps": step,
+                                                                                      "cache_hit": True}
                 if tup not in visited:
                     visited.add(tup)
                     total_nodes += 1
