@@ -43,9 +43,13 @@ def main():
                 if not ok:
                     continue
                 path = [(int(a), int(t)) for a, t in path]
-                expanded = vgs.expand_path_with_cyclic_reductions(pres, path) if cyc else path
-                out["expand"].append({"presentation": pres.tolist(), "cyclical": cyc, "compact": path,
-                                      "expanded": [[int(a), int(t)] for a, t in expanded]})
+                # a path found WITHOUT cyclic reduction is expanded too: the inserted conjugations change the states the
+                # later moves act on, so the result is whatever the reference computes (or the exception it raises)
+                try:
+                    expanded = [[int(a), int(t)] for a, t in vgs.expand_path_with_cyclic_reductions(pres, path)]
+                except (AssertionError, KeyError) as e:
+                    expanded = type(e).__name__
+                out["expand"].append({"presentation": pres.tolist(), "cyclical": cyc, "compact": path, "expanded": expanded})
                 solved.append((pres, cyc, path))
         for pres, cyc, path in solved[:12]:
             for rot in (False, True):
