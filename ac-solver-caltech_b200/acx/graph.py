@@ -84,7 +84,7 @@ class GraphEngine:
         self.ref = torch.empty((C,), dtype=torch.int64, device=d)
         self.csize = torch.empty((C,), dtype=torch.int16, device=d)
         self.flag = torch.empty((C,), dtype=torch.uint8, device=d)
-        self.excl = torch.empty((C,), dtype=torch.int64, device=d)
+        self.excl = torch.empty((C,), dtype=torch.int32, device=d)
         self.scan_tmp = torch.empty((self.be.scan_bytes(C),), dtype=torch.uint8, device=d)
         self.edges = torch.empty((C if self.want_edges else 1, 2), dtype=torch.int64, device=d)
         self.edge_filt = torch.empty((C if self.want_edges else 1,), dtype=torch.int16, device=d)

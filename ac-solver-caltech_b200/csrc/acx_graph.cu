@@ -20,14 +20,23 @@ __global__ void __launch_bounds__(256) k_graph_apply(int64_t n, const F f) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
 }
 
+template <class F>
+__global__ void k_graph_blocks(const F f) {
+    extern __shared__ uint4 g_smem[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(g_smem);
+    f.phase1((int64_t)blockIdx.x, (int)threadIdx.x, smem);
+    __syncthreads();
+    f.phase2((int64_t)blockIdx.x, (int)threadIdx.x, smem);
+}
+
 struct FlagToCount {
-    __host__ __device__ __forceinline__ int64_t operator()(const uint8_t& f) const { return (int64_t)f; }
+    __host__ __device__ __forceinline__ int32_t operator()(const uint8_t& f) const { return (int32_t)f; }
 };
 
 static int64_t scan_bytes(int64_t n) {
-    cub::TransformInputIterator<int64_t, FlagToCount, const uint8_t*> in(nullptr, FlagToCount());
+    cub::TransformInputIterator<int32_t, FlagToCount, const uint8_t*> in(nullptr, FlagToCount());
     size_t need = 0;
-    if (cub::DeviceScan::ExclusiveSum(nullptr, need, in, (int64_t*)nullptr, (int)n) != cudaSuccess) return -1;
+    if (cub::DeviceScan::ExclusiveSum(nullptr, need, in, (int32_t*)nullptr, (int)n) != cudaSuccess) return -1;
     return (int64_t)need;
 }
 
@@ -47,8 +56,19 @@ struct GpuExec {
     }
     template <class F>
     void run_shuffled(int64_t n, const F& f) { run(n, f); }
-    int scan(const uint8_t* flag, int64_t* excl, int64_t n, void* tmp, int64_t bytes) {
-        cub::TransformInputIterator<int64_t, FlagToCount, const uint8_t*> in(flag, FlagToCount());
+    template <class F>
+    void run_blocks(int64_t blocks, int threads, size_t smem, const F& f) {
+        if (blocks <= 0) return;
+        cudaError_t e = cudaSuccess;
+        if (smem > 48 * 1024) e = cudaFuncSetAttribute(k_graph_blocks<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) {
+            k_graph_blocks<F><<<(unsigned)blocks, threads, smem, stream>>>(f);
+            e = cudaGetLastError();
+        }
+        if (e != cudaSuccess && err == cudaSuccess) err = e;
+    }
+    int scan(const uint8_t* flag, int32_t* excl, int64_t n, void* tmp, int64_t bytes) {
+        cub::TransformInputIterator<int32_t, FlagToCount, const uint8_t*> in(flag, FlagToCount());
         size_t tb = (size_t)bytes;
         const cudaError_t e = cub::DeviceScan::ExclusiveSum(tmp, tb, in, excl, (int)n, stream);
         if (e != cudaSuccess) return acx_fail(ACX_ERR_CUDA, "acx_graph_step: cub::DeviceScan: %s", cudaGetErrorString(e));
@@ -101,7 +121,8 @@ extern "C" int acx_graph_step(const acx_graph_step_t* step, acx_stream_t stream)
     if (!a.nodes || !a.table || !a.cand || !a.ref || !a.csize || !a.flag || !a.excl || !a.scan_tmp || !a.node_size || !a.counts)
         return acx_fail(ACX_ERR_ARG, "acx_graph_step: null pointer");
     if (a.want_edges && (!a.edges || !a.edge_filt)) return acx_fail(ACX_ERR_ARG, "acx_graph_step: want_edges needs edges / edge_filt");
-    if (((uintptr_t)a.nodes | (uintptr_t)a.cand) & 15u) return acx_fail(ACX_ERR_ARG, "acx_graph_step: nodes / cand must be 16-byte aligned");
+    if (((uintptr_t)a.nodes | (uintptr_t)a.cand) & 31u) return acx_fail(ACX_ERR_ARG, "acx_graph_step: nodes / cand must be 32-byte aligned");
+    if (a.n_parents > 0x7FFFFFFFll * 32) return acx_fail(ACX_ERR_ARG, "acx_graph_step: too many parents for one launch");
     if (a.scan_tmp_bytes < scan_bytes(C)) return acx_fail(ACX_ERR_ARG, "acx_graph_step: scan scratch too small");
     GpuExec ex;
     if (int rc = make_exec(ex, stream)) return rc;
@@ -116,7 +137,7 @@ extern "C" int acx_graph_pack(const int8_t* rows, int64_t n, int m, const int32_
                               uint8_t* ok_out, acx_stream_t stream) {
     if (n < 0 || m < 1 || !width_ok(width_words)) return acx_fail(ACX_ERR_ARG, "acx_graph_pack: need n >= 0, m >= 1, width_words in {2,4,8}");
     if (n == 0) return ACX_OK;
-    if (!rows || !nodes_out || !ok_out || ((uintptr_t)nodes_out & 15u)) return acx_fail(ACX_ERR_ARG, "acx_graph_pack: null or unaligned pointer");
+    if (!rows || !nodes_out || !ok_out || ((uintptr_t)nodes_out & 31u)) return acx_fail(ACX_ERR_ARG, "acx_graph_pack: null or unaligned pointer");
     GpuExec ex;
     if (int rc = make_exec(ex, stream)) return rc;
     ACX_GRAPH_DISPATCH(width_words, ex.run(n, GPackRows<W>{rows, m, inst, nodes_out, ok_out}));
@@ -128,7 +149,7 @@ extern "C" int acx_graph_unpack(const uint32_t* nodes, int64_t n, int width_word
                                 acx_stream_t stream) {
     if (n < 0 || m < 1 || !width_ok(width_words)) return acx_fail(ACX_ERR_ARG, "acx_graph_unpack: need n >= 0, m >= 1, width_words in {2,4,8}");
     if (n == 0) return ACX_OK;
-    if (!nodes || !rows_out || ((uintptr_t)nodes & 15u)) return acx_fail(ACX_ERR_ARG, "acx_graph_unpack: null or unaligned pointer");
+    if (!nodes || !rows_out || ((uintptr_t)nodes & 31u)) return acx_fail(ACX_ERR_ARG, "acx_graph_unpack: null or unaligned pointer");
     GpuExec ex;
     if (int rc = make_exec(ex, stream)) return rc;
     ACX_GRAPH_DISPATCH(width_words, ex.run(n, GUnpackRows<W>{nodes, m, rows_out, inst_out}));
@@ -141,7 +162,7 @@ extern "C" int acx_graph_rehash(const uint32_t* nodes, int64_t n_nodes, int widt
     if (n_nodes < 0 || !width_ok(width_words) || tcap < 2 || (tcap & (tcap - 1)) || tcap < 2 * n_nodes)
         return acx_fail(ACX_ERR_ARG, "acx_graph_rehash: need a power-of-two table of at least 2 * n_nodes slots");
     if (n_nodes == 0) return ACX_OK;
-    if (!nodes || !table || ((uintptr_t)nodes & 15u)) return acx_fail(ACX_ERR_ARG, "acx_graph_rehash: null or unaligned pointer");
+    if (!nodes || !table || ((uintptr_t)nodes & 31u)) return acx_fail(ACX_ERR_ARG, "acx_graph_rehash: null or unaligned pointer");
     GpuExec ex;
     if (int rc = make_exec(ex, stream)) return rc;
     ACX_GRAPH_DISPATCH(width_words, ex.run(n_nodes, GRehash<W>{nodes, table, tcap}));
@@ -153,7 +174,7 @@ extern "C" int acx_graph_count_instances(const uint32_t* nodes, int64_t n_nodes,
                                          acx_stream_t stream) {
     if (n_nodes < 0 || n_inst < 1 || !width_ok(width_words)) return acx_fail(ACX_ERR_ARG, "acx_graph_count_instances: bad argument");
     if (n_nodes == 0) return ACX_OK;
-    if (!nodes || !counts || ((uintptr_t)nodes & 15u)) return acx_fail(ACX_ERR_ARG, "acx_graph_count_instances: null or unaligned pointer");
+    if (!nodes || !counts || ((uintptr_t)nodes & 31u)) return acx_fail(ACX_ERR_ARG, "acx_graph_count_instances: null or unaligned pointer");
     GpuExec ex;
     if (int rc = make_exec(ex, stream)) return rc;
     ACX_GRAPH_DISPATCH(width_words, ex.run(n_nodes, GCountInst<W>{nodes, counts, n_inst}));

@@ -59,11 +59,22 @@ struct GNode {
     uint32_t w[4 * W];
 };
 
+// Node / candidate access: 16*W bytes, 32-byte aligned (W is even).  On the device every 32 bytes move as ONE
+// 256-bit global access (a whole DRAM sector per request, sm_100).
 template <int W>
 ACX_HD GNode<W> g_load(const uint32_t* base, int64_t id) {
     GNode<W> o;
-    const uint4* p = reinterpret_cast<const uint4*>(base) + id * W;
+#ifdef __CUDA_ARCH__
+    const uint32_t* p = base + id * (4 * W);
 #pragma unroll
+    for (int i = 0; i < W / 2; ++i)
+        asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(o.w[8 * i]), "=r"(o.w[8 * i + 1]), "=r"(o.w[8 * i + 2]), "=r"(o.w[8 * i + 3]), "=r"(o.w[8 * i + 4]),
+                       "=r"(o.w[8 * i + 5]), "=r"(o.w[8 * i + 6]), "=r"(o.w[8 * i + 7])
+                     : "l"(p + 8 * i)
+                     : "memory");
+#else
+    const uint4* p = reinterpret_cast<const uint4*>(base) + id * W;
     for (int i = 0; i < W; ++i) {
         const uint4 v = p[i];
         o.w[4 * i] = v.x;
@@ -71,13 +82,22 @@ ACX_HD GNode<W> g_load(const uint32_t* base, int64_t id) {
         o.w[4 * i + 2] = v.z;
         o.w[4 * i + 3] = v.w;
     }
+#endif
     return o;
 }
 
 template <int W>
 ACX_HD void g_store(uint32_t* base, int64_t id, const GNode<W>& n) {
-    uint4* p = reinterpret_cast<uint4*>(base) + id * W;
+#ifdef __CUDA_ARCH__
+    uint32_t* p = base + id * (4 * W);
 #pragma unroll
+    for (int i = 0; i < W / 2; ++i)
+        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p + 8 * i), "r"(n.w[8 * i]), "r"(n.w[8 * i + 1]),
+                     "r"(n.w[8 * i + 2]), "r"(n.w[8 * i + 3]), "r"(n.w[8 * i + 4]), "r"(n.w[8 * i + 5]), "r"(n.w[8 * i + 6]),
+                     "r"(n.w[8 * i + 7])
+                     : "memory");
+#else
+    uint4* p = reinterpret_cast<uint4*>(base) + id * W;
     for (int i = 0; i < W; ++i) {
         uint4 v;
         v.x = n.w[4 * i];
@@ -86,6 +106,7 @@ ACX_HD void g_store(uint32_t* base, int64_t id, const GNode<W>& n) {
         v.w = n.w[4 * i + 3];
         p[i] = v;
     }
+#endif
 }
 
 template <int W>
@@ -186,38 +207,40 @@ ACX_HD int g_move(const GPres<W>& p, int k, bool classic, int cap, bool allow_em
     int tgt;
     Rel<W> x;
     bool ok = true;
+    const Rel<W>&r0 = p.r[0], &r1 = p.r[1];  // selects instead of indexed access: the relators stay in registers
     if (classic) {
         if (k < 4) {  // 0: (r1 r2, r2)  1: (r2 r1, r2)  2: (r1, r1 r2)  3: (r1, r2 r1)
             tgt = k >> 1;
-            x = p.r[k & 1];
-            ok = rel_concat<W>(x, p.r[(k & 1) ^ 1], cap);
+            const bool sw = (k & 1) != 0;
+            x = sw ? r1 : r0;
+            ok = rel_concat<W>(x, sw ? r0 : r1, cap);
         } else if (k < 12) {  // 4..7: conj0_(r2, a b A B)   8..11: conj0_(r1, a b A B)
             tgt = k < 8 ? 1 : 0;
             const int g = (k - 4) & 3;
-            x = p.r[tgt];
+            x = tgt ? r1 : r0;
             if (x.n > 0) ok = rel_conjugate<W>(x, g >= 2 ? 0u : 1u, (uint32_t)(g & 1), cap);
         } else {  // 12: inv0_(r1)   13: inv0_(r2)
             tgt = k - 12;
-            x = rel_inverse<W>(p.r[tgt]);
+            x = rel_inverse<W>(tgt ? r1 : r0);
         }
     } else {
         if (k < 4) {  // 0: (r1 r2, r2)  1: (r1, r2 r1)  2: (r1 r2^-1, r2)  3: (r1, r2 r1^-1)
             tgt = k & 1;
-            x = p.r[tgt];
-            Rel<W> o = p.r[tgt ^ 1];
+            x = tgt ? r1 : r0;
+            Rel<W> o = tgt ? r0 : r1;
             if (k >= 2) o = rel_inverse<W>(o);
             ok = rel_concat<W>(x, o, cap);
         } else {  // 4..7: conj0_(r1, B A a b)   8..11: conj0_(r2, B A a b)
             tgt = k < 8 ? 0 : 1;
             const int g = (k - 4) & 3;
-            x = p.r[tgt];
+            x = tgt ? r1 : r0;
             if (x.n > 0) ok = rel_conjugate<W>(x, g < 2 ? 0u : 1u, (g == 0 || g == 3) ? 1u : 0u, cap);
         }
     }
     if (!ok) return G_MOVE_OVERFLOW;
     if (x.n == 0 && !allow_empty) return G_MOVE_EMPTY;
-    c.r[tgt] = x;
-    c.r[tgt ^ 1] = p.r[tgt ^ 1];
+    c.r[0] = tgt ? r0 : x;
+    c.r[1] = tgt ? x : r1;
     c.inst = p.inst;
     g_sort<W>(c);
     return G_MOVE_OK;
@@ -324,22 +347,29 @@ struct GCountInst {
 
 // candidate c = (parent - parent_first) * n_moves + move: the position at which the reference's FIFO loop
 // reaches the child (ac_bfs.cpp:52-57), so "lowest c wins" reproduces its discovery order.
-// Work item i of the expand pass is laid out so that the 32 lanes of a warp apply the SAME move to 32 consecutive
-// parents (no divergence between the concat / conjugate / inverse paths, coalesced parent loads):
-//   i = (group * n_moves + move) * 32 + lane,  parent = group * 32 + lane.
+//
+// Expand pass: one block of 32 * n_moves threads per 32 consecutive parents.  Phase 1: warp k applies move k to the 32
+// parents (one move per warp: no divergence between the concat / conjugate / inverse paths; coalesced parent loads) and
+// parks the child in shared memory at its logical position lane * n_moves + k.  Phase 2: the block's candidates are one
+// contiguous range of the per-candidate arrays, written back with consecutive threads on consecutive entries (whole
+// sectors instead of 32 scattered 32-byte stores per instruction).
 static constexpr uint64_t G_FOUND = 1ull << 62;  // ref[c] = G_FOUND | node id: the child is a committed node
 
 template <int W>
 struct GExpand {
     acx_graph_step_t a;
     int nm;
-    ACX_HD void operator()(int64_t i) const {
-        const int lane = (int)(i & 31);
-        const int64_t gk = i >> 5;
-        const int k = (int)(gk % nm);
-        const int64_t local = (gk / nm) * 32 + lane;
-        if (local >= a.n_parents) return;
-        const int64_t c = local * nm + k;
+    ACX_HD static size_t smem_bytes(int nm) { return (size_t)32 * nm * (16 * W + 2); }
+    ACX_HD void phase1(int64_t block, int tid, uint8_t* smem) const {
+        const int lane = tid & 31, k = tid >> 5;
+        const int64_t local = block * 32 + lane;
+        uint32_t* scand = reinterpret_cast<uint32_t*>(smem);
+        uint16_t* ssize = reinterpret_cast<uint16_t*>(smem + (size_t)32 * nm * 16 * W);
+        const int j = lane * nm + k;
+        if (local >= a.n_parents) {
+            ssize[j] = 0;
+            return;
+        }
         const int cap = 32 * W - 8;
         const GPres<W> p = g_unpack<W>(g_load<W>(a.nodes, a.parent_first + local));
         GPres<W> ch;
@@ -360,9 +390,27 @@ struct GExpand {
             a.counts[2] = 1;
             skip = true;
         }
+        ssize[j] = skip ? (uint16_t)0 : (uint16_t)total;
+        if (!skip) {
+            const GNode<W> n = g_pack<W>(ch);
+#pragma unroll
+            for (int i = 0; i < 4 * W; ++i) scand[(size_t)j * 4 * W + i] = n.w[i];
+        }
+    }
+    ACX_HD void phase2(int64_t block, int tid, const uint8_t* smem) const {
+        const uint32_t* scand = reinterpret_cast<const uint32_t*>(smem);
+        const uint16_t* ssize = reinterpret_cast<const uint16_t*>(smem + (size_t)32 * nm * 16 * W);
+        const int64_t c = block * 32 * nm + tid;
+        if (c >= a.n_parents * nm) return;
+        const uint16_t sz = ssize[tid];
         a.ref[c] = -1;
-        a.csize[c] = skip ? (uint16_t)0 : (uint16_t)total;
-        if (!skip) g_store<W>(a.cand, c, g_pack<W>(ch));
+        a.csize[c] = sz;
+        if (sz) {
+            GNode<W> n;
+#pragma unroll
+            for (int i = 0; i < 4 * W; ++i) n.w[i] = scand[(size_t)tid * 4 * W + i];
+            g_store<W>(a.cand, c, n);
+        }
     }
 };
 
@@ -418,10 +466,10 @@ struct GResolve {  // flag = this candidate is the first discovery of a new stat
 
 struct GTotal {  // out[0] = number of flagged candidates
     const uint8_t* flag;
-    const int64_t* excl;
+    const int32_t* excl;
     int64_t n;
     int64_t* out;
-    ACX_HD void operator()(int64_t) const { out[0] = excl[n - 1] + (int64_t)flag[n - 1]; }
+    ACX_HD void operator()(int64_t) const { out[0] = (int64_t)excl[n - 1] + (int64_t)flag[n - 1]; }
 };
 
 // Winners become nodes in candidate order (ac_bfs.cpp:60-69: id = n_nodes + exclusive count of winners before c);
@@ -440,7 +488,7 @@ struct GCommitEdge {
             const int64_t r = a.ref[c];
             int64_t cc;
             if (win) {
-                cc = a.n_nodes + a.excl[c];
+                cc = a.n_nodes + (int64_t)a.excl[c];
                 g_store<W>(a.nodes, cc, g_load<W>(a.cand, c));
                 a.node_size[cc] = a.csize[c];
                 a.table[r] = (g_ld(a.table + r) & G_TAG) | (uint64_t)cc;
@@ -448,7 +496,7 @@ struct GCommitEdge {
                 cc = (int64_t)((uint64_t)r & G_VAL);
             } else {
                 const uint64_t e = g_ld(a.table + r);
-                cc = (e & G_PROV) ? a.n_nodes + a.excl[(int64_t)(e & G_VAL)] : (int64_t)(e & G_VAL);
+                cc = (e & G_PROV) ? a.n_nodes + (int64_t)a.excl[(int64_t)(e & G_VAL)] : (int64_t)(e & G_VAL);
             }
             a.ref[c] = cc;
             f = (a.parent_first + c / nm) < cc ? 1 : 0;
@@ -463,7 +511,7 @@ struct GEdgeWrite {
     int nm;
     ACX_HD void operator()(int64_t c) const {
         if (!a.flag[c]) return;
-        const int64_t pos = a.excl[c], par = a.parent_first + c / nm;
+        const int64_t pos = (int64_t)a.excl[c], par = a.parent_first + c / nm;
         a.edges[2 * pos] = par;
         a.edges[2 * pos + 1] = a.ref[c];
         const uint16_t ps = a.node_size[par], cs = a.csize[c];
@@ -474,13 +522,14 @@ struct GEdgeWrite {
 // One step: expand parents [parent_first, parent_first + n_parents), dedup against the table, append the new
 // nodes in discovery order and (optionally) emit the edge list of the step.
 // Exec::run(n, functor), Exec::run_shuffled(n, functor) (order-free functors; the host executor permutes them),
+// Exec::run_blocks(blocks, threads, smem bytes, functor with phase1 / phase2 separated by a block barrier),
 // Exec::scan(flag, excl, n, tmp, bytes).
 template <int W, class Exec>
 int graph_step(Exec& ex, const acx_graph_step_t& a) {
     const int nm = a.classic ? 14 : 12;
     const int64_t C = a.n_parents * nm;
     if (C == 0) return 0;
-    ex.run_shuffled(((a.n_parents + 31) / 32) * 32 * nm, GExpand<W>{a, nm});
+    ex.run_blocks((a.n_parents + 31) / 32, 32 * nm, GExpand<W>::smem_bytes(nm), GExpand<W>{a, nm});
     ex.run_shuffled(C, GProbe<W>{a});
     ex.run_shuffled(C, GResolve<W>{a});
     if (int rc = ex.scan(a.flag, a.excl, C, a.scan_tmp, a.scan_tmp_bytes)) return rc;

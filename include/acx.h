@@ -271,7 +271,7 @@ typedef struct acx_graph_step {
     int64_t* ref;        /* [C] claimed table slot / committed node id of every candidate */
     uint16_t* csize;     /* [C] */
     uint8_t* flag;       /* [C] */
-    int64_t* excl;       /* [C] */
+    int32_t* excl;       /* [C] exclusive counts of the two stream compactions (C < 2^31) */
     void* scan_tmp;      /* acx_graph_scan_bytes(C) bytes */
     int64_t scan_tmp_bytes;
     /* outputs */

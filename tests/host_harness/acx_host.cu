@@ -128,8 +128,20 @@ struct HostExec {
             for (int64_t i = 0; i < n; ++i) f((int64_t)(((__int128)i * step) % n));
         }
     }
-    int scan(const uint8_t* flag, int64_t* excl, int64_t n, void*, int64_t) {
-        int64_t run = 0;
+    // one block at a time: phase1 for every thread, then phase2 (what the barrier guarantees); the thread order inside a
+    // phase follows g_order
+    template <class F>
+    void run_blocks(int64_t blocks, int threads, size_t smem_bytes, const F& f) {
+        std::vector<uint64_t> smem(smem_bytes / 8 + 2);
+        uint8_t* sm = reinterpret_cast<uint8_t*>(smem.data());
+        for (int64_t b = 0; b < blocks; ++b) {
+            const int64_t bb = g_order == 1 ? blocks - 1 - b : b;
+            run_shuffled(threads, [&](int64_t t) { f.phase1(bb, (int)t, sm); });
+            run_shuffled(threads, [&](int64_t t) { f.phase2(bb, (int)t, sm); });
+        }
+    }
+    int scan(const uint8_t* flag, int32_t* excl, int64_t n, void*, int64_t) {
+        int32_t run = 0;
         for (int64_t i = 0; i < n; ++i) {
             excl[i] = run;
             run += flag[i];
