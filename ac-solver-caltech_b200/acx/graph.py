@@ -102,14 +102,14 @@ class GraphEngine:
     def _reserve(self, extra):
         need = self.n_nodes + extra
         if need > self.capacity:
-            cap = max(need, 4 * self.capacity, 1 << 16)  # few growth events: each is an allocation, a copy and a rehash
-            nodes = torch.zeros((cap, 4 * self.W), dtype=torch.int32, device=self.be.dev)
-            size = torch.zeros((cap,), dtype=torch.int16, device=self.be.dev)
+            cap = max(need, 2 * self.capacity, 1 << 16)
+            nodes = torch.empty((cap, 4 * self.W), dtype=torch.int32, device=self.be.dev)
+            size = torch.empty((cap,), dtype=torch.int16, device=self.be.dev)
             nodes[: self.n_nodes].copy_(self.nodes[: self.n_nodes])
             size[: self.n_nodes].copy_(self.node_size[: self.n_nodes])
             self.nodes, self.node_size, self.capacity = nodes, size, cap
         if self.tcap < 2 * need:
-            self.tcap = _next_pow2(8 * need)
+            self.tcap = _next_pow2(4 * need)
             self.table = torch.zeros((self.tcap,), dtype=torch.int64, device=self.be.dev)
             self.be.call("rehash", self.nodes.data_ptr(), self.n_nodes, self.W, self.table.data_ptr(), self.tcap)
 
