@@ -13,7 +13,7 @@ LEVEL_SYNCHRONOUS_FROM = 1 << 16
 def bfs(presentation, max_nodes_to_explore=10000, verbose=False, cyclically_reduce_after_moves=False):
     """FIFO search.  Returns (True, path) or (False, None) (breadth_first.py:84-97)."""
     row = np.array(presentation, dtype=np.int8)
-    if max_nodes_to_explore >= LEVEL_SYNCHRONOUS_FROM and row.shape[0] % 4 == 0:
+    if max_nodes_to_explore >= LEVEL_SYNCHRONOUS_FROM:
         stats = {}
         ok, path = _level.bfs_level(row, max_nodes_to_explore, cyclically_reduce_after_moves, str(_device.device()), stats=stats)
         n_seen = stats["n_seen"]

@@ -58,8 +58,6 @@ def beam_search(presentation, model, architecture="mlp", feat_mean=None, feat_st
     root = np.ascontiguousarray(np.asarray(presentation), dtype=np.int8)
     rowb = len(root)
     m = rowb // 2
-    if rowb % 4:
-        raise ValueError("beam_search on the GPU needs an even max_relator_length")
     if solution_cache is not None:  # :459-465
         cached = _check_cache_with_rotations(tuple(int(v) for v in root), m, solution_cache)
         if cached is not None:
@@ -175,8 +173,6 @@ def value_guided_greedy_search(presentation, model=None, architecture="mlp", fea
     root = np.ascontiguousarray(np.asarray(presentation), dtype=np.int8)
     rowb = len(root)
     m = rowb // 2
-    if rowb % 4:
-        raise ValueError("value_guided_greedy_search on the GPU needs an even max_relator_length")
     dev = torch.device(device)
     stream = _prep(dev)
     L = _lib.lib()

@@ -21,8 +21,6 @@ class LevelBFS:
     def __init__(self, root, budget, cyclical=False, device="cuda:0", chunk=1 << 20):
         root = np.ascontiguousarray(np.asarray(root), dtype=np.int8)
         self.m = len(root) // 2
-        if (2 * self.m) % 4:
-            raise ValueError("the level-synchronous bfs needs an even max_relator_length")
         self.rowb = 2 * self.m
         self.budget = max(1, int(budget))
         self.cyc = bool(cyclical)

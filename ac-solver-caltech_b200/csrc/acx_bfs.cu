@@ -45,6 +45,36 @@ __device__ __forceinline__ bool bfs_rows_equal(const uint32_t* a, const uint32_t
     return d == 0u;
 }
 
+// Rows of any width (the single-GPU level engine, beam / value-guided search): 2m % 4 == 0 reads 32-bit words, other
+// widths (AK(2) at max_relator_length = 7, the reference tests' example) assemble the same words from bytes, the last
+// one zero-filled.  rowb is a kernel parameter, so the branch is uniform.
+__device__ __forceinline__ uint32_t bfs_word_b(const int8_t* row, int k, int rowb) {
+    uint32_t w = 0;
+    for (int b = 0; b < 4; ++b) {
+        const int i = 4 * k + b;
+        if (i < rowb) w |= (uint32_t)(uint8_t)row[i] << (8 * b);
+    }
+    return w;
+}
+
+__device__ __forceinline__ uint64_t bfs_row_hash_any(const int8_t* row, int rowb) {
+    if ((rowb & 3) == 0) return bfs_row_hash(reinterpret_cast<const uint32_t*>(row), rowb / 4);
+    uint64_t h = 0x9E3779B97F4A7C15ull;
+    for (int k = 0; k < (rowb + 3) / 4; ++k) {
+        h ^= bfs_word_b(row, k, rowb);
+        h *= 0xFF51AFD7ED558CCDull;
+        h ^= h >> 29;
+    }
+    return h;
+}
+
+__device__ __forceinline__ bool bfs_rows_equal_any(const int8_t* a, const int8_t* b, int rowb) {
+    if ((rowb & 3) == 0) return bfs_rows_equal(reinterpret_cast<const uint32_t*>(a), reinterpret_cast<const uint32_t*>(b), rowb / 4);
+    int d = 0;
+    for (int k = 0; k < rowb; ++k) d |= a[k] ^ b[k];
+    return d == 0;
+}
+
 struct ProbeParams {
     const int8_t* cand;       // [n, rowb] candidate rows of this round
     const uint8_t* lens;      // [n, 2]
@@ -65,8 +95,7 @@ struct ProbeParams {
 __global__ void k_bfs_probe(const ProbeParams p) {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= p.n) return;
-    const int nwords = p.rowb / 4;
-    const uint32_t* row = reinterpret_cast<const uint32_t*>(p.cand + j * p.rowb);
+    const int8_t* row = p.cand + j * p.rowb;
     const int64_t ord = p.order ? p.order[j] : j;
     if (p.status && p.status[j] != 0) {
         atomicMin(p.min_error, (unsigned long long)ord);
@@ -78,7 +107,7 @@ __global__ void k_bfs_probe(const ProbeParams p) {
         p.slot_out[j] = -2;
         return;
     }
-    const uint64_t h = bfs_row_hash(row, nwords);
+    const uint64_t h = bfs_row_hash_any(row, p.rowb);
     if (p.hash_out) p.hash_out[j] = h;
     const uint64_t tag = ((h >> 48) | 1ull) << 48;
     const uint64_t mine = tag | PROV_BIT | (uint64_t)j;
@@ -103,7 +132,7 @@ __global__ void k_bfs_probe(const ProbeParams p) {
                         p.slot_out[j] = (int64_t)slot;
                         return;
                     }
-                    if (!bfs_rows_equal(row, reinterpret_cast<const uint32_t*>(p.cand + other * p.rowb), nwords)) break;
+                    if (!bfs_rows_equal_any(row, p.cand + other * p.rowb, p.rowb)) break;
                     const int64_t oord = p.order ? p.order[other] : other;
                     if (oord < ord) {  // it stays; we are a duplicate within the round (resolved in phase 2)
                         p.slot_out[j] = (int64_t)slot;
@@ -120,7 +149,7 @@ __global__ void k_bfs_probe(const ProbeParams p) {
                 }
             } else {
                 const int64_t id = (int64_t)(e & VAL_MASK);
-                if (bfs_rows_equal(row, reinterpret_cast<const uint32_t*>(p.nodes + id * p.rowb), nwords)) {
+                if (bfs_rows_equal_any(row, p.nodes + id * p.rowb, p.rowb)) {
                     p.slot_out[j] = -1;
                     return;
                 }
@@ -169,10 +198,13 @@ __global__ void k_bfs_commit(const CommitParams p) {
     if (!p.is_new[j]) return;
     if (j >= p.limit) return;  // beyond the cut: the search ends here
     const int64_t id = p.node_base + p.new_rank[j];
-    const int nwords = p.rowb / 4;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(p.cand + j * p.rowb);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(p.nodes + id * p.rowb);
-    for (int k = 0; k < nwords; ++k) dst[k] = src[k];
+    if ((p.rowb & 3) == 0) {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(p.cand + j * p.rowb);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(p.nodes + id * p.rowb);
+        for (int k = 0; k < p.rowb / 4; ++k) dst[k] = src[k];
+    } else {
+        for (int k = 0; k < p.rowb; ++k) p.nodes[id * p.rowb + k] = p.cand[j * p.rowb + k];
+    }
     const int64_t ord = p.order ? p.order[j] : j;
     p.parent[id] = p.parent_base + ord / 12;
     p.action[id] = (uint8_t)(ord % 12);
@@ -184,13 +216,12 @@ __global__ void k_bfs_commit(const CommitParams p) {
 __global__ void k_rows_hash(const int8_t* rows, int64_t n, int rowb, uint64_t* out) {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
-    out[j] = bfs_row_hash(reinterpret_cast<const uint32_t*>(rows + j * rowb), rowb / 4);
+    out[j] = bfs_row_hash_any(rows + j * rowb, rowb);
 }
 
 // root insertion
 __global__ void k_bfs_seed(const int8_t* row, int rowb, uint64_t* table, int64_t tcap, int64_t id) {
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(row);
-    const uint64_t h = bfs_row_hash(w, rowb / 4);
+    const uint64_t h = bfs_row_hash_any(row, rowb);
     const uint64_t tag = ((h >> 48) | 1ull) << 48;
     const uint64_t mask = (uint64_t)tcap - 1;
     uint64_t slot = (h ^ (h >> 23)) & mask;
@@ -585,7 +616,7 @@ static int launch_expand_bucket(const int8_t* nodes, const int64_t* loc, const i
 using namespace acx;
 
 extern "C" int acx_bfs_seed(const int8_t* row, int m, uint64_t* table, int64_t tcap, int64_t node_id, acx_stream_t stream) {
-    if (!row || !table || m < 1 || (2 * m) % 4 != 0 || tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_bfs_seed: bad argument (m must be even, tcap a power of two)");
+    if (!row || !table || m < 1 || tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_bfs_seed: bad argument (tcap must be a power of two)");
     k_bfs_seed<<<1, 1, 0, (cudaStream_t)stream>>>(row, 2 * m, table, tcap, node_id);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
@@ -594,7 +625,7 @@ extern "C" int acx_bfs_seed(const int8_t* row, int m, uint64_t* table, int64_t t
 extern "C" int acx_bfs_probe(const int8_t* cand, const uint8_t* lens, const uint8_t* status, const int64_t* order, int64_t n,
                              int m, uint64_t* table, int64_t tcap, const int8_t* nodes, int64_t* slot_out,
                              uint64_t* min_success, uint64_t* min_error, uint64_t* hash_out, uint8_t* is_new_out, acx_stream_t stream) {
-    if (n < 0 || m < 1 || (2 * m) % 4 != 0 || tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe: bad argument (m must be even, tcap a power of two)");
+    if (n < 0 || m < 1 || tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe: bad argument (tcap must be a power of two)");
     if (n == 0) return ACX_OK;
     if (!cand || !lens || !table || !nodes || !slot_out || !min_success || !min_error || !is_new_out) return acx_fail(ACX_ERR_ARG, "acx_bfs_probe: null pointer");
     ProbeParams p;
@@ -614,7 +645,7 @@ extern "C" int acx_bfs_commit(const int8_t* cand, const uint8_t* lens, const int
                               const int64_t* new_rank, const int64_t* order, int64_t parent_base, int64_t n, int64_t limit,
                               int m, uint64_t* table, int8_t* nodes, int64_t* parent, uint8_t* action, uint16_t* total,
                               int64_t node_base, acx_stream_t stream) {
-    if (n < 0 || m < 1 || (2 * m) % 4 != 0) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit: bad argument");
+    if (n < 0 || m < 1) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit: bad argument");
     if (n == 0) return ACX_OK;
     if (!cand || !lens || !slot || !is_new || !new_rank || !table || !nodes || !parent || !action || !total) return acx_fail(ACX_ERR_ARG, "acx_bfs_commit: null pointer");
     CommitParams p;
@@ -627,7 +658,7 @@ extern "C" int acx_bfs_commit(const int8_t* cand, const uint8_t* lens, const int
 }
 
 extern "C" int acx_rows_hash(const int8_t* rows, int64_t n, int m, uint64_t* hash_out, acx_stream_t stream) {
-    if (n < 0 || m < 1 || (2 * m) % 4 != 0) return acx_fail(ACX_ERR_ARG, "acx_rows_hash: bad argument (m must be even)");
+    if (n < 0 || m < 1) return acx_fail(ACX_ERR_ARG, "acx_rows_hash: bad argument");
     if (n == 0) return ACX_OK;
     if (!rows || !hash_out) return acx_fail(ACX_ERR_ARG, "acx_rows_hash: null pointer");
     k_rows_hash<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rows, n, 2 * m, hash_out);

@@ -59,8 +59,6 @@ def test_value_guided_greedy_search_with_cache(cuda, golden):
     hits = 0
     for case in golden["search"]:
         pres = np.array(case["presentation"], dtype=np.int8)
-        if len(pres) % 4:  # the level engine behind the search needs an even max_relator_length (AK(2) at m = 7)
-            continue
         sub = {k: v for k, v in cache.items() if len(k) == len(pres)}
         ok, path, stats = value_guided_greedy_search(pres, use_length_priority=True, max_nodes_to_explore=3000, solution_cache=sub,
                                                      device=str(cuda))
@@ -87,8 +85,6 @@ def test_beam_search_with_cache(cuda, golden, oracle):
     hits = 0
     for case in golden["search"]:
         pres = np.array(case["presentation"], dtype=np.int8)
-        if len(pres) % 4:
-            continue
         sub = {k: v for k, v in cache.items() if len(k) == len(pres)}
         for width, budget in ((8, 1500), (1, 60)):
             want = _beam_oracle(oracle, pres, model, "mlp", mean, std, width, budget, cuda, False, cache=sub)
