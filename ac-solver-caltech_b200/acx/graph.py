@@ -291,6 +291,31 @@ def neighbourhood_sizes(presentations, radius=5, classic=True, width_words=None,
     return out
 
 
+def neighbourhood_sizes_sharded(presentations, radius=5, classic=True, device=None, _backend=None, **kw):
+    """neighbourhood_sizes over the ranks of an initialised torch.distributed group (one process per GPU): balls are
+    independent, so rank r simply takes presentations r, r + world, ... -- no data-path collective -- and the sizes meet
+    in one all-gather.  Every rank returns the full int64 [n] array."""
+    import torch.distributed as dist
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    n = len(presentations)
+    if device is None:
+        device = "cuda:%d" % torch.cuda.current_device() if torch.cuda.is_available() else "cpu"
+    mine = list(range(rank, n, world))
+    local = neighbourhood_sizes([presentations[i] for i in mine], radius, classic, device=device, _backend=_backend, **kw)
+    per = (n + world - 1) // world
+    comm_dev = torch.device(device) if dist.get_backend() == "nccl" else torch.device("cpu")
+    buf = torch.full((per,), -1, dtype=torch.int64, device=comm_dev)
+    buf[: len(mine)] = torch.from_numpy(local).to(comm_dev)
+    parts = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(parts, buf)
+    out = np.zeros((n,), dtype=np.int64)
+    for r, part in enumerate(parts):
+        idx = list(range(r, n, world))
+        out[idx] = part[: len(idx)].cpu().numpy()
+    return out
+
+
 _LETTER = {1: "a", -1: "A", 2: "b", -2: "B"}
 
 
