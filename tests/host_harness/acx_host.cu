@@ -217,3 +217,31 @@ extern "C" int acxh_path_expand_cyclic(const int8_t* roots, const uint8_t* actio
     }
     return 0;
 }
+
+// one move of the graph engine (g_move + sort) on byte rows, for a direct comparison with the oracle's Presentation::move
+template <int W>
+static void graph_move_rows(const int8_t* rows, int64_t n, int m, const uint8_t* moves, int classic, int allow_empty, int8_t* out,
+                            int32_t* status) {
+    std::vector<uint32_t> node(4 * W + 8);
+    std::vector<uint8_t> ok(1);
+    for (int64_t j = 0; j < n; ++j) {
+        // 32-byte aligned scratch is not needed on the host path of g_load / g_store
+        GPackRows<W>{rows + j * 2 * m, m, nullptr, node.data(), ok.data()}(0);
+        if (!ok[0]) {
+            status[j] = -1;
+            continue;
+        }
+        const GPres<W> p = g_unpack<W>(g_load<W>(node.data(), 0));
+        GPres<W> c;
+        status[j] = g_move<W>(p, moves[j], classic != 0, 32 * W - 8, allow_empty != 0, c);
+        if (status[j] != G_MOVE_OK) continue;
+        g_store<W>(node.data(), 0, g_pack<W>(c));
+        GUnpackRows<W>{node.data(), m, out + j * 2 * m, nullptr}(0);
+    }
+}
+
+extern "C" int acxh_graph_move(const int8_t* rows, int64_t n, int m, const uint8_t* moves, int classic, int allow_empty, int w,
+                               int8_t* out, int32_t* status) {
+    ACXH_DISPATCH(w, (graph_move_rows<W>(rows, n, m, moves, classic, allow_empty, out, status)));
+    return 0;
+}

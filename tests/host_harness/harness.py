@@ -42,6 +42,7 @@ def lib():
         L.acxh_graph_rehash.argtypes = [_P, _I64, _I32, _P, _I64, _P]
         L.acxh_graph_count_instances.argtypes = [_P, _I64, _I32, _P, _I64, _P]
         L.acxh_ms_enumerate.argtypes = [_I32, _I64, _I64, _P, _P, _P]
+        L.acxh_graph_move.argtypes = [_P, _I64, _I32, _P, _I32, _I32, _I32, _P, _P]
         L.acxh_path_expand_cyclic.argtypes = [_P, _P, _P, _I64, _I32, _I32, _P, _P, _I32, _P, _P, _P, _P]
         _lib = L
     return _lib
@@ -106,3 +107,16 @@ class HostExpandBackend:
 
     def expand(self, *args):
         assert self.L.acxh_path_expand_cyclic(*args, None) == 0
+
+
+def graph_move(rows, moves, classic, width_words, allow_empty=False):
+    """g_move + sort of csrc/acx_graph.cuh on byte rows [n, 2m]: (children int8 [n, 2m], status int32 [n])
+    (status 0 ok, 1 relator over the plane capacity, 2 empty relator, -1 row outside the domain)."""
+    rows = np.ascontiguousarray(rows, dtype=np.int8)
+    mv = np.ascontiguousarray(moves, dtype=np.uint8)
+    out = np.zeros_like(rows)
+    st = np.zeros(len(rows), dtype=np.int32)
+    rc = lib().acxh_graph_move(rows.ctypes.data, len(rows), rows.shape[1] // 2, mv.ctypes.data, int(bool(classic)),
+                               int(bool(allow_empty)), width_words, out.ctypes.data, st.ctypes.data)
+    assert rc == 0
+    return out, st

@@ -86,6 +86,61 @@ def test_domain_errors():
     assert graph.neighbourhood_sizes([long], 2, True, _backend=be).tolist() == [bo.neighbourhood(long, 2, True)]
 
 
+@pytest.mark.parametrize("width,maxlen", [(2, 27), (4, 59), (8, 123)])
+def test_single_moves_equal_oracle_on_long_relators(width, maxlen):
+    """g_move (multi-word plane shifts, junction cancellation of any depth, sort_) against Presentation::move of the
+    oracle on random reduced words up to the plane capacity, incl. pairs built to cancel deeply."""
+    from helpers import reduced_word
+
+    rng = np.random.default_rng(width)
+    cap = 32 * width - 8
+    m = cap + 8
+    rows, moves = [], []
+    for k in range(3000):
+        la, lb = int(rng.integers(1, maxlen + 1)), int(rng.integers(1, maxlen + 1))
+        a, b = reduced_word(rng, la), reduced_word(rng, lb)
+        kind = k % 4
+        if kind == 1:  # b starts with the inverse of a's tail: deep cancellation in a.b
+            t = int(rng.integers(1, min(la, lb) + 1))
+            b = [-v for v in reversed(a[-t:])] + b[t:]
+        elif kind == 2:  # b ends with the inverse of a's head: deep cancellation in b.a
+            t = int(rng.integers(1, min(la, lb) + 1))
+            b = b[:-t] + [-v for v in reversed(a[:t])]
+        for w in (a, b):  # keep both freely reduced
+            i = 0
+            while i + 1 < len(w):
+                if w[i] == -w[i + 1]:
+                    del w[i:i + 2]
+                    i = max(i - 1, 0)
+                else:
+                    i += 1
+        if not a or not b:
+            continue
+        row = np.zeros(2 * m, dtype=np.int8)
+        row[:len(a)] = a
+        row[m:m + len(b)] = b
+        rows.append(row)
+        moves.append(int(rng.integers(0, 14)))
+    rows = np.stack(rows)
+    for classic in (True, False):
+        mv = np.array(moves) % (14 if classic else 12)
+        got, st = harness.graph_move(rows, mv, classic, width, allow_empty=True)
+        n_ok = 0
+        for j in range(len(rows)):
+            want = bo.move(rows[j], int(mv[j]), classic)
+            if want is None:  # empty relator (the oracle's row form cannot hold it) or longer than m
+                continue
+            child, size = want
+            a_len, b_len = np.count_nonzero(child[:m]), np.count_nonzero(child[m:])
+            if max(a_len, b_len) > cap:
+                assert st[j] == 1, j
+                continue
+            assert st[j] == 0, (j, st[j])
+            assert np.array_equal(got[j], child), (width, classic, j, int(mv[j]))
+            n_ok += 1
+        assert n_ok > 2000
+
+
 def test_product_backend_needs_cuda():
     import torch
 
