@@ -51,7 +51,8 @@ _SIGNATURES = {
     "acx_peer_export": (_I32, [_PTR, _PTR]),
     "acx_peer_open": (_I32, [_PTR, _PTR]),
     "acx_peer_close": (_I32, [_PTR]),
-    "acx_env_step": (_I32, [_PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _I64, _I32, _I32, _F32, _F32, _I32, _PTR]),
+    "acx_env_step": (_I32, [_PTR, _PTR]),
+    "acx_env_meta_init": (_I32, [_PTR, _PTR, _PTR, _I64, _I32, _PTR]),
     "acx_rows_certify": (_I32, [_PTR, _I64, _I32, _PTR, _PTR, _PTR]),
     "acx_graph_scan_bytes": (_I64, [_I64]),
     "acx_graph_step": (_I32, [_PTR, _PTR]),
@@ -61,6 +62,21 @@ _SIGNATURES = {
     "acx_graph_count_instances": (_I32, [_PTR, _I64, _I32, _PTR, _I64, _PTR]),
     "acx_ms_enumerate": (_I32, [_I32, _I64, _I64, _PTR, _PTR, _PTR]),
 }
+
+
+class EnvIO(ctypes.Structure):
+    """acx_env_io of include/acx.h (field for field)"""
+
+    _fields_ = [
+        ("state", _PTR), ("meta", _PTR), ("actions", _PTR), ("step_out", _PTR), ("reward_clipped", _PTR),
+        ("row_status", _PTR), ("err_count", _PTR), ("pool", _PTR), ("next_idx", _PTR), ("action_ring", _PTR),
+        ("t", _I64), ("ring_len", ctypes.c_int32), ("fin_cap", ctypes.c_int32), ("fin_count", _PTR), ("fin_env", _PTR),
+        ("fin_steps", _PTR), ("fin_state", _PTR), ("chain", _PTR), ("n", _I64), ("m", ctypes.c_int32),
+        ("horizon", ctypes.c_int32), ("clip_lo", _F32), ("clip_hi", _F32), ("flags", ctypes.c_int32),
+    ]
+
+
+ENV_CERTIFIED, ENV_CHAINED, ENV_CHAIN_SLOTS = 1, 2, 4096
 
 
 class AcxError(RuntimeError):

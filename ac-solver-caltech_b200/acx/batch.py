@@ -77,45 +77,90 @@ def certify(rows, lens_out=None):
 
 
 class EnvBuffers:
-    """Device-resident state of N lockstep ACEnv instances (ac_env.py:53-89 fields, as arrays)."""
+    """Device-resident state of N lockstep ACEnv instances (ac_env.py:53-89 fields, as arrays):
+    state int8 [N, 2m] and one 32-bit word per env, meta = count_steps | len0 << 16 | len1 << 24.
 
-    def __init__(self, state, horizon, pool=None):
+    want_clip / want_status: allocate the optional per-row outputs (clipped float reward, row status); without
+    them the step writes the 8-byte record only and errors are reported through `err_count`.
+    track_actions: keep the action ring (uint8 [horizon, N]) and the finished-episode side buffer on the device --
+    what `ACEnv.actions` / gymnasium's final_info hold in the reference (ac_env.py:92,110)."""
+
+    def __init__(self, state, horizon, pool=None, want_clip=True, want_status=True, track_actions=False, fin_cap=None):
         n, row = state.shape
         self.n, self.m = n, row // 2
         self.horizon = int(horizon)
+        if not 1 <= self.horizon <= 65535:
+            raise ValueError("horizon_length must be in 1..65535 (count_steps is a 16-bit field of the env word)")
         dev = state.device
         self.state = state.contiguous()
-        self.steps = torch.zeros(n, dtype=torch.int32, device=dev)
+        self.meta = torch.zeros(n, dtype=torch.int32, device=dev)
         # one 8-byte record per env written by the kernel: int32 reward | done | truncated | len0 | len1
         self.step_out = torch.zeros((n, 8), dtype=torch.uint8, device=dev)
         self.reward = self.step_out.view(torch.int32)[:, 0]
         self.done = self.step_out[:, 4]
         self.truncated = self.step_out[:, 5]
         self.lens = self.step_out[:, 6:8]
-        self.reward_clipped = torch.empty(n, dtype=torch.float32, device=dev)
-        # certification: when every state and pool row is certified the kernel skips its input checks
-        self.certified = certify(self.state, self.step_out[:, 6:8])
-        if self.certified and pool is not None:
-            self.certified = certify(pool.contiguous(), None)
-        self.status = torch.empty(n, dtype=torch.uint8, device=dev)
+        self.reward_clipped = torch.empty(n, dtype=torch.float32, device=dev) if want_clip else None
+        self.status = torch.zeros(n, dtype=torch.uint8, device=dev) if want_status else None
+        self.err_count = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.chain = torch.zeros(_lib.ENV_CHAIN_SLOTS, dtype=torch.int32, device=dev)
         self.pool = None if pool is None else pool.contiguous()
+        self.t = 0  # number of steps taken (selects the ring row)
+        self.ring = self.fin_count = self.fin_env = self.fin_steps = self.fin_state = None
+        self.fin_cap = 0
+        if track_actions:
+            self.ring = torch.zeros((self.horizon, n), dtype=torch.uint8, device=dev)
+            self.fin_cap = int(fin_cap if fin_cap is not None else n)
+            self.fin_count = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.fin_env = torch.zeros(self.fin_cap, dtype=torch.int32, device=dev)
+            self.fin_steps = torch.zeros(self.fin_cap, dtype=torch.int32, device=dev)
+            self.fin_state = torch.zeros((self.fin_cap, row), dtype=torch.int8, device=dev)
+        self._recertify()
+
+    def _recertify(self, steps=None):
+        """lengths -> meta (count_steps kept unless given) and certification of the states and the pool: when every
+        row is certified the kernel skips its input checks"""
+        keep = (self.meta & 0xFFFF) if steps is None else steps.to(torch.int32)
+        self.certified = certify(self.state, self.step_out[:, 6:8])
+        if self.certified and self.pool is not None:
+            self.certified = certify(self.pool, None)
+        stream = _prep(self.state.device)
+        keep = keep.contiguous()
+        _lib.check(_lib.lib().acx_env_meta_init(_ptr(self.state), _ptr(keep), _ptr(self.meta), self.n, self.m, stream),
+                   "acx_env_meta_init")
+
+    @property
+    def steps(self):
+        """count_steps of every env (a copy: the counters live in the low 16 bits of `meta`)"""
+        return (self.meta & 0xFFFF).to(torch.int32)
+
+    def set_steps(self, steps):
+        self.meta.copy_((self.meta & ~0xFFFF) | (steps.to(torch.int32) & 0xFFFF))
+
+    def set_state(self, state, steps=None):
+        """Overwrite the env states (and optionally step counters); lengths and certification are redone."""
+        self.state.copy_(state)
+        self._recertify(steps)
+
+    def set_row(self, i, row, steps=0):
+        """env i <- row (ACEnv.reset with a starting_state, ac_env.py:113-129)"""
+        self.state[i].copy_(row)
+        m = self.m
+        l0, l1 = int((row[:m] != 0).sum()), int((row[m:] != 0).sum())
+        word = (int(steps) & 0xFFFF) | (l0 << 16) | (l1 << 24)
+        self.meta[i] = word - (1 << 32) if word >= (1 << 31) else word
+        self.step_out[i, 6] = l0
+        self.step_out[i, 7] = l1
+        if self.certified and not certify(row[None, :].contiguous()):
+            self.certified = False  # an arbitrary starting state: back to the checked kernel
 
 
-def _set_state(self, state, steps=None):
-    """Overwrite the env states (and optionally step counters); lengths and certification are redone."""
-    self.state.copy_(state)
-    if steps is not None:
-        self.steps.copy_(steps)
-    self.certified = certify(self.state, self.step_out[:, 6:8])
-    if self.certified and self.pool is not None:
-        self.certified = certify(self.pool, None)
+def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0), chained=False):
+    """ACEnv.step over all envs in place (ac_env.py:91-111) + reset of finished envs from buf.pool.
 
-
-EnvBuffers.set_state = _set_state
-
-
-def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0)):
-    """ACEnv.step over all envs in place (ac_env.py:91-111) + reset of finished envs from buf.pool."""
+    chained=True promises that `actions` (and next_idx) were complete before the previous env_step on this buffer
+    was launched and that nothing else wrote its state in between: consecutive steps then overlap head-to-tail
+    (acx.h: ACX_ENV_CHAINED)."""
     _chk(actions, torch.uint8, (buf.n,), "actions")
     stream = _prep(buf.state.device)
     pool = buf.pool if next_idx is not None else None
@@ -123,9 +168,20 @@ def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0)):
         _chk(next_idx, torch.int32, (buf.n,), "next_idx")
         if pool is None:
             raise ValueError("next_idx given but the env buffers hold no pool")
-    rc = _lib.lib().acx_env_step(_ptr(buf.state), _ptr(buf.steps), _ptr(actions), _ptr(pool), _ptr(next_idx),
-                                 _ptr(buf.step_out), _ptr(buf.reward_clipped), _ptr(buf.status), buf.n, buf.m,
-                                 buf.horizon, float(clip[0]), float(clip[1]),
-                                 1 if buf.certified else 0, stream)
+    io = _lib.EnvIO()
+    io.state, io.meta, io.actions, io.step_out = _ptr(buf.state), _ptr(buf.meta), _ptr(actions), _ptr(buf.step_out)
+    io.reward_clipped, io.row_status, io.err_count = _ptr(buf.reward_clipped), _ptr(buf.status), _ptr(buf.err_count)
+    io.pool, io.next_idx = _ptr(pool), _ptr(next_idx)
+    io.action_ring, io.t, io.ring_len = _ptr(buf.ring), buf.t, buf.horizon
+    io.fin_cap, io.fin_count, io.fin_env = buf.fin_cap, _ptr(buf.fin_count), _ptr(buf.fin_env)
+    io.fin_steps, io.fin_state = _ptr(buf.fin_steps), _ptr(buf.fin_state)
+    io.chain = _ptr(buf.chain)
+    io.n, io.m, io.horizon = buf.n, buf.m, buf.horizon
+    io.clip_lo, io.clip_hi = float(clip[0]), float(clip[1])
+    io.flags = (_lib.ENV_CERTIFIED if buf.certified else 0) | (_lib.ENV_CHAINED if chained else 0)
+    import ctypes
+
+    rc = _lib.lib().acx_env_step(ctypes.addressof(io), stream)
     _lib.check(rc, "acx_env_step")
+    buf.t += 1
     return buf

@@ -17,8 +17,7 @@
 
 #include "../../include/acx.h"
 #include "acx_common.h"
-#include "acx_rows.cuh"
-#include "acx_tma.cuh"
+#include "acx_envtile.cuh"
 
 namespace acx {
 
@@ -32,15 +31,7 @@ struct StepParams {
     int64_t row0;  // first row handled by this launch
     int m;
     int cyclical;
-    // ACEnv.step extras (ENV kernels)
-    int32_t* steps;
-    uint8_t* step_out;  // [n, 8]: int32 reward | u8 done | u8 truncated | u8 len0 | u8 len1
-    float* reward_clipped;
-    const int8_t* pool;
-    const int32_t* next_idx;
-    int horizon;
-    float clip_lo, clip_hi;
-    int certified;  // ACX_ENV_CERTIFIED: rows are certified and step_out holds their lengths
+    EnvParams env;  // ACEnv.step extras (ENV kernels)
 };
 
 // m <= 64 takes the 64-bit plane path, wider rows the generic multi-word planes
@@ -50,42 +41,17 @@ __device__ __forceinline__ void row_move(uint8_t* srow, int m, int move, bool cy
     else acmove_row<W, MS>(srow, srow, m, move, cyc, l0, l1, status);
 }
 
-// ac_env.py:97-111 on one row that already sits (post-move) in shared memory
+// per-row outputs of the checked kernels (the certified tile kernel stages them in shared memory instead)
 template <bool ENV>
 __device__ __forceinline__ void row_epilogue(const StepParams& p, int64_t row, uint8_t* srow, int m, int l0, int l1,
-                                             uint32_t status, int32_t steps_in) {
+                                             uint32_t status, uint32_t meta_in, int move) {
     if (ENV) {
-        const int total = l0 + l1;
-        bool done = false;
-        if (total == 2) {  // is_presentation_trivial (utils.py:57-87): |letters| == {1,2}
-            int a = (int8_t)srow[0], b = (int8_t)srow[m];
-            a = a < 0 ? -a : a;
-            b = b < 0 ? -b : b;
-            done = (a == 1 && b == 2) || (a == 2 && b == 1);
-        }
-        const int32_t max_reward = p.horizon * m * 2;    // ac_env.py:76
-        const int32_t rew = done ? max_reward : -total;  // ac_env.py:100
-        const int32_t steps = steps_in + 1;              // ac_env.py:102
-        const bool trunc = steps >= p.horizon;           // ac_env.py:103
-        if (p.reward_clipped) p.reward_clipped[row] = fminf(fmaxf((float)rew, p.clip_lo), p.clip_hi);
-        int32_t steps_out = steps;
-        if (p.pool && (done || trunc)) {  // ac_env.py:113-129 via agents/training.py:351-352
-            const int8_t* src = p.pool + (int64_t)p.next_idx[row] * 2 * m;
-            int c0 = 0, c1 = 0;
-            for (int k = 0; k < m; ++k) {
-                const int8_t v0 = src[k], v1 = src[m + k];
-                srow[k] = (uint8_t)v0;
-                srow[m + k] = (uint8_t)v1;
-                c0 += v0 != 0;
-                c1 += v1 != 0;
-            }
-            l0 = c0;
-            l1 = c1;
-            steps_out = 0;
-        }
-        p.steps[row] = steps_out;
-        const uint32_t hi = (done ? 1u : 0u) | (trunc ? 0x100u : 0u) | ((uint32_t)l0 << 16) | ((uint32_t)l1 << 24);
-        reinterpret_cast<uint2*>(p.step_out)[row] = make_uint2((uint32_t)rew, hi);
+        const EnvParams& e = p.env;
+        const EnvOut o = env_finish(e, row, srow, m, l0, l1, status, meta_in & 0xFFFFu);
+        e.meta[row] = o.meta;
+        reinterpret_cast<uint2*>(e.step_out)[row] = make_uint2(o.rew, o.hi);
+        if (e.reward_clipped) e.reward_clipped[row] = o.clip;
+        if (e.ring_row) e.ring_row[row] = (uint8_t)move;
     } else {
         if (p.lens) *reinterpret_cast<uchar2*>(p.lens + 2 * row) = make_uchar2((uint8_t)l0, (uint8_t)l1);
     }
@@ -93,7 +59,7 @@ __device__ __forceinline__ void row_epilogue(const StepParams& p, int64_t row, u
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int W, int MS, int TR, int S, bool ENV, bool CERT>
+template <int W, int MS, int TR, int S, bool ENV>
 __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t ntiles) {
     constexpr int ROWB = 2 * MS;
     constexpr uint32_t TILEB = (uint32_t)TR * ROWB;
@@ -135,21 +101,15 @@ __global__ void __launch_bounds__(TR) k_rows_tma(const StepParams p, int64_t nti
     for (int64_t t = first; t < ntiles; t += stride) {
         const int64_t row = p.row0 + t * TR + tid;
         const int move = p.actions[row];
-        int32_t steps_in = 0;
-        if (ENV) steps_in = p.steps[row];
+        uint32_t meta_in = 0;
+        if (ENV) meta_in = p.env.meta[row];
         int l0 = 0, l1 = 0;
-        if (CERT) {  // lengths of a certified env row = the record the previous step left
-            const uchar2 ln = *reinterpret_cast<const uchar2*>(p.step_out + 8 * row + 6);
-            l0 = ln.x;
-            l1 = ln.y;
-        }
         mbar_wait(bar0 + 8 * s, parity);
 
         uint8_t* srow = my_rows + s * TILEB;
         uint32_t status;
-        if constexpr (CERT) status = acmove_row64_certified<MS>(srow, move, l0, l1);
-        else row_move<W, MS>(srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
-        row_epilogue<ENV>(p, row, srow, MS, l0, l1, status, steps_in);
+        row_move<W, MS>(srow, MS, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
+        row_epilogue<ENV>(p, row, srow, MS, l0, l1, status, meta_in, move);
 
         fence_proxy_async();
         __syncthreads();
@@ -202,13 +162,13 @@ __global__ void __launch_bounds__(TR) k_rows_simple(const StepParams p, int64_t 
     if (tid < rows) {
         const int64_t row = p.row0 + r0 + tid;
         const int move = p.actions[row];
-        int32_t steps_in = 0;
-        if (ENV) steps_in = p.steps[row];
+        uint32_t meta_in = 0;
+        if (ENV) meta_in = p.env.meta[row];
         uint8_t* srow = smem + (size_t)tid * rowb;
         int l0, l1;
         uint32_t status;
         row_move<W, MS>(srow, m, move, ENV ? true : (p.cyclical != 0), l0, l1, status);
-        row_epilogue<ENV>(p, row, srow, m, l0, l1, status, steps_in);
+        row_epilogue<ENV>(p, row, srow, m, l0, l1, status, meta_in, move);
     }
     __syncthreads();
     coop_copy(gout, smem, rows * rowb, tid, TR);
@@ -269,10 +229,34 @@ static int sm_count() {
     return cached[dev];
 }
 
-template <int W, int MS, int TR, int S, bool ENV, bool CERT>
+static int pdl_enabled() {
+    static const int pdl = [] {
+        const char* e = getenv("ACX_PDL");
+        return e ? atoi(e) : 1;
+    }();
+    return pdl;
+}
+
+template <typename Kern, typename Params>
+static int launch_pdl(Kern kern, int64_t grid, int block, size_t smem, cudaStream_t st, const Params& p, int64_t ntiles) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    ACX_CUDA(cudaLaunchKernelEx(&cfg, kern, p, ntiles));
+    return ACX_OK;
+}
+
+template <int W, int MS, int TR, int S, bool ENV>
 static int launch_tma(const StepParams& p, int64_t ntiles, cudaStream_t st) {
     constexpr size_t smem = (size_t)S * TR * 2 * MS + 8 * S;
-    auto kern = k_rows_tma<W, MS, TR, S, ENV, CERT>;
+    auto kern = k_rows_tma<W, MS, TR, S, ENV>;
     static int ctas_per_sm[ACX_MAX_DEVICES] = {0};  // function attributes are per device
     const int dev = current_device();
     if (ctas_per_sm[dev] == 0) {
@@ -282,22 +266,27 @@ static int launch_tma(const StepParams& p, int64_t ntiles, cudaStream_t st) {
         ctas_per_sm[dev] = occ > 0 ? occ : 1;
     }
     const int64_t grid = std::min<int64_t>(ntiles, (int64_t)sm_count() * ctas_per_sm[dev]);
-    static const int pdl = [] {
-        const char* e = getenv("ACX_PDL");
-        return e ? atoi(e) : 1;
-    }();
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)grid);
-    cfg.blockDim = dim3(TR);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
-    ACX_CUDA(cudaLaunchKernelEx(&cfg, kern, p, ntiles));
-    return ACX_OK;
+    return launch_pdl(kern, grid, TR, smem, st, p, ntiles);
+}
+
+// certified env rows (m = 36): the class-sorted tile kernel of acx_envtile.cuh
+template <int MS, int TR, int S>
+static int launch_env_tiles(EnvParams e, int64_t ntiles, bool whole_batch, cudaStream_t st) {
+    constexpr size_t smem = EnvTile<MS, TR>::smem_bytes(S);
+    auto kern = k_env_tiles<MS, TR, S>;
+    static int ctas_per_sm[ACX_MAX_DEVICES] = {0};
+    const int dev = current_device();
+    if (ctas_per_sm[dev] == 0) {
+        ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 0;
+        ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TR, smem));
+        ctas_per_sm[dev] = occ > 0 ? occ : 1;
+    }
+    const int64_t grid = std::min<int64_t>(ntiles, (int64_t)sm_count() * ctas_per_sm[dev]);
+    // the per-CTA dependency replaces the grid-wide one only when this launch is the whole step
+    if (grid > ACX_ENV_CHAIN_SLOTS) e.chain = nullptr;
+    if (!e.chain || !whole_batch || !pdl_enabled()) e.chain_wait = 0;
+    return launch_pdl(kern, grid, TR, smem, st, e, ntiles);
 }
 
 template <int W, int MS, int TR, bool ENV>
@@ -317,23 +306,59 @@ static int launch_simple(const StepParams& p, int64_t nrows, cudaStream_t st) {
     return ACX_OK;
 }
 
-// rows [0, n): full tiles through the bulk-copy kernel when a static instantiation exists and the
+static int env_tile_rows() {  // ACX_ENV_TILE=128|256 (tuning knob)
+    static int v = 0;
+    if (v == 0) {
+        const char* e = getenv("ACX_ENV_TILE");
+        v = e ? atoi(e) : 128;
+        if (v != 256) v = 128;
+    }
+    return v;
+}
+
+static int env_stages() {  // ACX_ENV_STAGES=2|3|4 (tuning knob)
+    static int v = 0;
+    if (v == 0) {
+        const char* e = getenv("ACX_ENV_STAGES");
+        v = e ? atoi(e) : 3;
+        if (v < 2 || v > 4) v = 3;
+    }
+    return v;
+}
+
+static bool env_tiles_usable(const EnvParams& e) {
+    uintptr_t a = (uintptr_t)e.state | (uintptr_t)e.meta | (uintptr_t)e.actions | (uintptr_t)e.step_out |
+                  (uintptr_t)e.reward_clipped | (uintptr_t)e.status | (uintptr_t)e.ring_row;
+    return (a & 15u) == 0;
+}
+
+// rows [0, n): full tiles through a bulk-copy kernel when a static instantiation exists and the
 // buffers are 16-byte aligned; everything else through the simple kernel.
 template <int W, int MS, int TR, int S, bool ENV>
-static int run_static(StepParams p, cudaStream_t st) {
+static int run_static(StepParams p, bool certified, cudaStream_t st) {
     const bool aligned = (((uintptr_t)p.in | (uintptr_t)p.out) & 15u) == 0;
     int64_t done_rows = 0;
-    if (aligned && p.n >= TR) {
+    if constexpr (ENV && MS == 36) {
+        if (certified && env_tiles_usable(p.env)) {
+            const int tr = env_tile_rows(), stg = env_stages();
+            if (p.n >= tr) {
+                const int64_t ntiles = p.n / tr;
+                const bool whole = ntiles * tr == p.n;
+                EnvParams e = p.env;
+                e.row0 = 0;
+                int rc;
+                if (tr == 256) rc = stg == 2 ? launch_env_tiles<36, 256, 2>(e, ntiles, whole, st) : launch_env_tiles<36, 256, 3>(e, ntiles, whole, st);
+                else rc = stg == 2 ? launch_env_tiles<36, 128, 2>(e, ntiles, whole, st)
+                        : stg == 4 ? launch_env_tiles<36, 128, 4>(e, ntiles, whole, st) : launch_env_tiles<36, 128, 3>(e, ntiles, whole, st);
+                if (rc) return rc;
+                done_rows = ntiles * tr;
+            }
+        }
+    }
+    if (done_rows == 0 && aligned && p.n >= TR) {
         const int64_t ntiles = p.n / TR;
         p.row0 = 0;
-        int rc;
-        if constexpr (ENV && W <= 2) {
-            rc = p.certified ? launch_tma<W, MS, TR, S, ENV, true>(p, ntiles, st)
-                             : launch_tma<W, MS, TR, S, ENV, false>(p, ntiles, st);
-        } else {
-            rc = launch_tma<W, MS, TR, S, ENV, false>(p, ntiles, st);
-        }
-        if (rc) return rc;
+        if (int rc = launch_tma<W, MS, TR, S, ENV>(p, ntiles, st)) return rc;
         done_rows = ntiles * TR;
     }
     if (done_rows < p.n) {
@@ -363,20 +388,32 @@ static int tile_rows() {  // ACX_TILE=64|128|256 (tuning knob; default 128)
 }
 
 template <bool ENV>
-static int run_rows(StepParams p, cudaStream_t st) {
+static int run_rows(StepParams p, bool certified, cudaStream_t st) {
     if (p.n == 0) return ACX_OK;
     p.row0 = 0;
     switch (p.m) {
         case 36:
-            if (tile_rows() == 256) return run_static<2, 36, 256, 3, ENV>(p, st);
-            if (tile_rows() == 64) return run_static<2, 36, 64, 4, ENV>(p, st);
-            return tma_stages() == 3 ? run_static<2, 36, 128, 3, ENV>(p, st) : run_static<2, 36, 128, 4, ENV>(p, st);
-        case 128: return run_static<4, 128, 64, 4, ENV>(p, st);
+            if (tile_rows() == 256) return run_static<2, 36, 256, 3, ENV>(p, certified, st);
+            if (tile_rows() == 64) return run_static<2, 36, 64, 4, ENV>(p, certified, st);
+            return tma_stages() == 3 ? run_static<2, 36, 128, 3, ENV>(p, certified, st) : run_static<2, 36, 128, 4, ENV>(p, certified, st);
+        case 128: return run_static<4, 128, 64, 4, ENV>(p, certified, st);
         default: break;
     }
     if (p.m <= 32) return launch_simple<1, 0, 128, ENV>(p, p.n, st);
     if (p.m <= 64) return launch_simple<2, 0, 128, ENV>(p, p.n, st);
     return launch_simple<4, 0, 64, ENV>(p, p.n, st);
+}
+
+__global__ void k_env_meta_init(const int8_t* state, const int32_t* steps, uint32_t* meta, int64_t n, int m) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    const int8_t* r = state + row * 2 * m;
+    uint32_t l0 = 0, l1 = 0;
+    for (int k = 0; k < m; ++k) {
+        l0 += r[k] != 0;
+        l1 += r[m + k] != 0;
+    }
+    meta[row] = ((steps ? (uint32_t)steps[row] : 0u) & 0xFFFFu) | (l0 << 16) | (l1 << 24);
 }
 
 }  // namespace acx
@@ -397,36 +434,69 @@ extern "C" int acx_move_batch(const int8_t* states_in, const uint8_t* moves, int
     p.n = n;
     p.m = m;
     p.cyclical = cyclical;
-    return run_rows<false>(p, (cudaStream_t)stream);
+    return run_rows<false>(p, false, (cudaStream_t)stream);
 }
 
-extern "C" int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
-                            const int32_t* next_idx, uint8_t* step_out, float* reward_clipped, uint8_t* row_status,
-                            int64_t n, int m, int horizon, float clip_lo, float clip_hi, int flags, acx_stream_t stream) {
-    if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH || horizon < 1)
-        return acx_fail(ACX_ERR_ARG, "acx_env_step: need n >= 0, 1 <= m <= 128, horizon >= 1");
-    if (n > 0 && (!state || !steps || !actions || !step_out)) return acx_fail(ACX_ERR_ARG, "acx_env_step: null pointer");
-    if (((uintptr_t)step_out & 7u) != 0) return acx_fail(ACX_ERR_ARG, "acx_env_step: step_out must be 8-byte aligned");
-    if ((pool == nullptr) != (next_idx == nullptr)) return acx_fail(ACX_ERR_ARG, "acx_env_step: pool and next_idx go together");
+extern "C" int acx_env_step(const acx_env_io* io, acx_stream_t stream) {
+    if (!io) return acx_fail(ACX_ERR_ARG, "acx_env_step: null io");
+    const int64_t n = io->n;
+    const int m = io->m;
+    if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH || io->horizon < 1 || io->horizon > 65535)
+        return acx_fail(ACX_ERR_ARG, "acx_env_step: need n >= 0, 1 <= m <= 128, 1 <= horizon <= 65535");
+    if (n > 0 && (!io->state || !io->meta || !io->actions || !io->step_out)) return acx_fail(ACX_ERR_ARG, "acx_env_step: null pointer");
+    if (((uintptr_t)io->step_out & 7u) != 0 || ((uintptr_t)io->meta & 3u) != 0)
+        return acx_fail(ACX_ERR_ARG, "acx_env_step: step_out must be 8-byte aligned, meta 4-byte aligned");
+    if ((io->pool == nullptr) != (io->next_idx == nullptr)) return acx_fail(ACX_ERR_ARG, "acx_env_step: pool and next_idx go together");
+    if (io->action_ring && io->ring_len < 1) return acx_fail(ACX_ERR_ARG, "acx_env_step: action_ring needs ring_len >= 1");
+    if (io->fin_count && (!io->fin_env || !io->fin_steps || !io->fin_state || io->fin_cap < 0))
+        return acx_fail(ACX_ERR_ARG, "acx_env_step: fin_count needs fin_env, fin_steps, fin_state and fin_cap >= 0");
+    if (n > 0x7FFFFFFFll && io->fin_count) return acx_fail(ACX_ERR_ARG, "acx_env_step: fin_env holds 32-bit env indices");
     StepParams p;
     memset(&p, 0, sizeof p);
-    p.in = state;
-    p.out = state;
-    p.actions = actions;
-    p.status = row_status;
+    p.in = io->state;
+    p.out = io->state;
+    p.actions = io->actions;
+    p.status = io->row_status;
     p.n = n;
     p.m = m;
     p.cyclical = 1;
-    p.steps = steps;
-    p.step_out = step_out;
-    p.reward_clipped = reward_clipped;
-    p.pool = pool;
-    p.next_idx = next_idx;
-    p.horizon = horizon;
-    p.clip_lo = clip_lo;
-    p.clip_hi = clip_hi;
-    p.certified = (flags & ACX_ENV_CERTIFIED) ? 1 : 0;
-    return run_rows<true>(p, (cudaStream_t)stream);
+    EnvParams& e = p.env;
+    e.state = io->state;
+    e.meta = io->meta;
+    e.actions = io->actions;
+    e.step_out = io->step_out;
+    e.reward_clipped = io->reward_clipped;
+    e.status = io->row_status;
+    e.pool = io->pool;
+    e.next_idx = io->next_idx;
+    if (io->action_ring) {
+        int64_t slot = io->t % io->ring_len;
+        if (slot < 0) slot += io->ring_len;
+        e.ring_row = io->action_ring + slot * n;
+    }
+    e.fin_count = io->fin_count;
+    e.fin_env = io->fin_env;
+    e.fin_steps = io->fin_steps;
+    e.fin_state = io->fin_state;
+    e.fin_cap = io->fin_cap;
+    e.err_count = io->err_count;
+    e.chain = io->chain;
+    e.chain_wait = (io->chain && (io->flags & ACX_ENV_CHAINED)) ? 1 : 0;
+    e.n = n;
+    e.m = m;
+    e.horizon = io->horizon;
+    e.clip_lo = io->clip_lo;
+    e.clip_hi = io->clip_hi;
+    return run_rows<true>(p, (io->flags & ACX_ENV_CERTIFIED) != 0, (cudaStream_t)stream);
+}
+
+extern "C" int acx_env_meta_init(const int8_t* state, const int32_t* steps, uint32_t* meta, int64_t n, int m, acx_stream_t stream) {
+    if (n < 0 || m < 1 || m > ACX_MAX_RELATOR_LENGTH) return acx_fail(ACX_ERR_ARG, "acx_env_meta_init: need n >= 0, 1 <= m <= 128");
+    if (n == 0) return ACX_OK;
+    if (!state || !meta) return acx_fail(ACX_ERR_ARG, "acx_env_meta_init: null pointer");
+    k_env_meta_init<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(state, steps, meta, n, m);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
 }
 
 extern "C" int acx_rows_primitive(const int8_t* states_in, const uint8_t* moves, int8_t* states_out, uint8_t* lens_out,

@@ -30,7 +30,15 @@ ACX_HD uint32_t fshr_c(uint32_t lo, uint32_t hi, int s) { return __funnelshift_r
 ACX_HD uint32_t brev32(uint32_t x) { return __brev(x); }
 ACX_HD int clz32(uint32_t x) { return __clz(x); }
 ACX_HD int popc32(uint32_t x) { return __popc(x); }
+ACX_HD uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) { return __byte_perm(a, b, sel); }
 #else
+// byte permute: result byte i = byte (selector nibble i & 7) of the 8-byte pool {b, a} (no sign replication used)
+ACX_HD uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    const uint64_t pool = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) r |= (uint32_t)((pool >> (8 * ((sel >> (4 * i)) & 7u))) & 0xFFu) << (8 * i);
+    return r;
+}
 ACX_HD uint32_t fshl(uint32_t lo, uint32_t hi, int s) {
     s &= 31;
     return (uint32_t)(((((uint64_t)hi) << 32 | lo) << s) >> 32);

@@ -230,16 +230,18 @@ def gpu_arm(args):
     bufs, acts, nxts = [], [], []
     for b in range(N_BATCHES):
         states = walk_states_gpu(pool, n, seed=100 * rank + b, dev=dev)
-        bufs.append(batch.EnvBuffers(states, HORIZON, pool=pool))
+        bufs.append(batch.EnvBuffers(states, HORIZON, pool=pool, want_clip=False, want_status=False))
         assert bufs[-1].certified, "bench states must be certified rows"
-        bufs[-1].steps.copy_(torch.randint(0, HORIZON, (n,), device=dev, generator=g, dtype=torch.int32))
+        bufs[-1].set_steps(torch.randint(0, HORIZON, (n,), device=dev, generator=g, dtype=torch.int32))
         acts.append(torch.randint(0, 12, (n,), device=dev, generator=g, dtype=torch.int64).to(torch.uint8))
         nxts.append(torch.randint(0, pool.shape[0], (n,), device=dev, generator=g, dtype=torch.int32))
     before = bufs[0].state.clone()
 
+    chained = os.environ.get("ACX_BENCH_CHAINED", "1") != "0"
+
     def step(k):
         b = k % N_BATCHES
-        batch.env_step(bufs[b], acts[(k // N_BATCHES) % N_BATCHES], next_idx=nxts[b])
+        batch.env_step(bufs[b], acts[(k // N_BATCHES) % N_BATCHES], next_idx=nxts[b], chained=chained)
 
     def barrier():
         if world > 1:

@@ -75,20 +75,67 @@ int acx_rows_primitive(const int8_t* states_in, const uint8_t* moves, int8_t* st
  * max_reward = horizon*m*2 (:76), count_steps += 1, truncated = count_steps >= horizon), fused
  * with the reset the PPO loop applies to finished envs (ACEnv.reset, ac_env.py:113-129;
  * agents/training.py:351-352): when pool != NULL and done|truncated, state <- pool[next_idx[e]],
- * steps <- 0.
- * step_out [n] is one 8-byte record per env (8-byte aligned):
+ * count_steps <- 0.
+ *
+ * Persistent state of env e: state[e] (2m int8, the reference's own row) and ONE 32-bit word
+ *     meta[e] = count_steps (bits 0..15) | len(r_0) << 16 | len(r_1) << 24        (horizon <= 65535)
+ * (ACEnv.count_steps / ACEnv.lengths, ac_env.py:84-88).  acx_rows_certify / acx_env_meta_init fill it.
+ * step_out [n] is one 8-byte record per env (16-byte aligned array), written every step:
  *     int32 reward | uint8 done | uint8 truncated | uint8 len(r_0) | uint8 len(r_1)
  * (lengths are those of the state left in `state`, i.e. after a reset if one happened).
- * reward_clipped (optional, float [n]) = clip(reward, clip_lo, clip_hi), the TransformReward
- * wrapper of agents/environment.py:48-52.  row_status [n] may be NULL.
+ * Optional outputs (NULL = off):
+ *   reward_clipped float [n]   clip(reward, clip_lo, clip_hi): TransformReward, agents/environment.py:48-52
+ *   row_status uint8 [n]       ACX_ROW_STATUS_* of every row, written every step
+ *   err_count int32 [1]        += number of rows with a non-zero status (the reference raises for them,
+ *                              utils.py:264-266; here the row keeps its state) -- one word to poll
+ *   action_ring uint8 [ring_len, n]  row (t % ring_len) <- actions: the device-side action log
+ *                              (ACEnv.actions, ac_env.py:92); with ring_len >= horizon the actions of a
+ *                              finished episode of length L are ring[(t-L+1 .. t) % ring_len, e]
+ *   fin_*                      finished-episode side buffer: for every env that is done|truncated in this
+ *                              step, k = (*fin_count)++ and, if k < fin_cap, fin_env[k] = e, fin_steps[k] =
+ *                              its episode length, fin_state[k] = its final state BEFORE the reset
+ *                              (gymnasium's final_observation / final_info, agents/training.py:273-280)
  * flags: ACX_ENV_CERTIFIED promises that every row of `state` and of `pool` is certified
  * (acx_rows_certify said so, or the row is the output of an earlier acx_env_step on certified rows)
- * and that step_out[e].len0/len1 hold the current lengths of env e (acx_rows_certify writes them);
- * the kernel then skips the per-row input checks.  Results are identical either way. */
+ * and that meta holds the current lengths; the kernel then skips the per-row input checks (m = 36:
+ * kernel k_env_tiles, every array through bulk copies; arrays 16-byte aligned).  Results are identical
+ * either way.
+ * chain (optional, ACX_ENV_CHAIN_SLOTS zeroed uint32, one set per env batch): every launch of the certified
+ * kernel keeps a parity counter per CTA there.  ACX_ENV_CHAINED additionally promises that every input of this
+ * step other than state/meta (actions, pool, next_idx) was complete before the PREVIOUS acx_env_step on these
+ * buffers was launched and that nothing else touched state/meta in between; CTA b then waits for CTA b of the
+ * previous launch only (the exact row dependency) instead of the whole grid, so consecutive steps overlap
+ * head-to-tail.  Without the flag the step is ordered after everything earlier in the stream, as usual. */
 #define ACX_ENV_CERTIFIED 1
-int acx_env_step(int8_t* state, int32_t* steps, const uint8_t* actions, const int8_t* pool,
-                 const int32_t* next_idx, uint8_t* step_out, float* reward_clipped, uint8_t* row_status,
-                 int64_t n, int m, int horizon, float clip_lo, float clip_hi, int flags, acx_stream_t stream);
+#define ACX_ENV_CHAINED 2
+#define ACX_ENV_CHAIN_SLOTS 4096
+typedef struct acx_env_io {
+    int8_t* state;           /* [n, 2m] in place */
+    uint32_t* meta;          /* [n] in place */
+    const uint8_t* actions;  /* [n] move ids 0..11 */
+    uint8_t* step_out;       /* [n, 8] */
+    float* reward_clipped;   /* [n] or NULL */
+    uint8_t* row_status;     /* [n] or NULL */
+    int32_t* err_count;      /* [1] or NULL */
+    const int8_t* pool;      /* [P, 2m] or NULL */
+    const int32_t* next_idx; /* [n] or NULL (goes with pool) */
+    uint8_t* action_ring;    /* [ring_len, n] or NULL */
+    int64_t t;               /* index of this step (selects the ring row) */
+    int32_t ring_len;
+    int32_t fin_cap;
+    int32_t* fin_count;      /* [1] or NULL */
+    int32_t* fin_env;        /* [fin_cap] */
+    int32_t* fin_steps;      /* [fin_cap] */
+    int8_t* fin_state;       /* [fin_cap, 2m] */
+    uint32_t* chain;         /* [ACX_ENV_CHAIN_SLOTS] or NULL */
+    int64_t n;
+    int32_t m, horizon;
+    float clip_lo, clip_hi;
+    int32_t flags;
+} acx_env_io;
+int acx_env_step(const acx_env_io* io /* host struct */, acx_stream_t stream);
+/* meta[e] = steps[e] (NULL = 0) | lengths of state[e] (non-zero counts per half): after writing states by hand */
+int acx_env_meta_init(const int8_t* state, const int32_t* steps, uint32_t* meta, int64_t n, int m, acx_stream_t stream);
 
 /* Row certification for the env fast path: certified_out[r] = 1 iff row r has letters in {0,+-1,+-2},
  * zeros only as right padding, and both relators freely and cyclically reduced (every output of

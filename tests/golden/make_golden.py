@@ -19,6 +19,7 @@ Files:
                         budget exit) on AK(2), AK(3), the MS cases of the reference's
                         search tests and random dataset rows
   env_golden.npz        ACEnv.step trajectories (obs, reward, done, truncated, lengths)
+  env_info_golden.json  info["actions"] of the reference ACEnv at every done of those trajectories (target envinfo)
   greedy10k.json        BASELINE config #1: greedy_search on all 1190 rows at
                         max_nodes_to_explore=10000 (solved flag + path)
 """
@@ -284,6 +285,28 @@ def make_env(ref):
     np.savez_compressed(os.path.join(HERE, "env_golden.npz"), init=init, horizon=horizon, actions=actions,
                         obs=obs, reward=reward, done=done, truncated=trunc, lens=lens)
     print("env:", E, "envs x", T, "steps;", int(done.sum()), "done,", int(trunc.sum()), "truncated")
+
+
+def make_envinfo(ref):
+    """info["actions"] of the reference ACEnv (ac_env.py:92,110) at every `done` of the env_golden.npz trajectories:
+    the same envs are re-run on the recorded actions with the reset-on-finish of agents/training.py:351-352."""
+    g = np.load(os.path.join(HERE, "env_golden.npz"))
+    init, horizon, actions = g["init"], g["horizon"], g["actions"]
+    events = []
+    for e in range(init.shape[0]):
+        env = ref.ACEnv(ref.ACEnvConfig(initial_state=init[e].copy(), horizon_length=int(horizon[e])))
+        for t in range(actions.shape[0]):
+            o, r, d, tr, info = env.step(int(actions[t, e]))
+            assert np.array_equal(o, g["obs"][t, e]) and bool(d) == bool(g["done"][t, e])
+            if d:
+                events.append({"t": t, "env": e, "actions": [int(a) for a in info["actions"]], "final_obs": jsonable(o)})
+            else:
+                assert info == {}
+            if d or tr:
+                env.reset()
+    with open(os.path.join(HERE, "env_info_golden.json"), "w") as f:
+        json.dump({"events": events}, f, separators=(",", ":"))
+    print("envinfo:", len(events), "done events with action lists")
 
 
 def _greedy_job(args):

@@ -7,7 +7,7 @@
 
 #include <vector>
 
-#include "../../ac-solver-caltech_b200/csrc/acx_rows.cuh"
+#include "../../ac-solver-caltech_b200/csrc/acx_envrow.cuh"
 
 using namespace acx;
 
@@ -67,14 +67,41 @@ static void run_cert36(const int8_t* in, const uint8_t* moves, int8_t* out, uint
     }
 }
 
+// class-split certified step of the env tile kernel (csrc/acx_envrow.cuh): conjugations on the bytes,
+// concatenations on planes.  The scratch row is padded like the kernel's stage (the byte path reads the
+// word in front of a relator); `junk` fills the padding so that nothing depends on it.
+static void run_cert36_split(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status, int64_t n,
+                             uint8_t junk) {
+    const int m = 36, rowb = 72;
+    std::vector<uint64_t> a(rowb / 8 + 4);
+    for (int64_t r = 0; r < n; ++r) {
+        memset(a.data(), junk, a.size() * 8);
+        uint8_t* ia = reinterpret_cast<uint8_t*>(a.data()) + 8;
+        memcpy(ia, in + r * rowb, rowb);
+        int l0 = -1, l1 = -1;
+        uint32_t st = 99;
+        if (row_is_certified(ia, m, l0, l1)) st = cert_row_step<36>(ia, moves[r], l0, l1);
+        else acmove_row64<36>(ia, m, moves[r], true, l0, l1, st);
+        memcpy(out + r * rowb, ia, rowb);
+        lens[2 * r] = (uint8_t)l0;
+        lens[2 * r + 1] = (uint8_t)l1;
+        status[r] = (uint8_t)st;
+    }
+}
+
 // variant: 0 = dynamic width (generic planes), 1 = static generic planes (m must be 36 or 128),
 //          2 = 64-bit planes dynamic (m <= 64), 3 = 64-bit planes static (m == 36),
-//          4 = certified-row env path (m == 36, cyclical only)
+//          4 = certified-row env path (m == 36, cyclical only), 5/6 = class-split certified step (acx_envrow.cuh)
 extern "C" int acxh_move_batch(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status,
                                int64_t n, int m, int cyc, int variant, int inplace) {
     if (variant == 4) {
         if (m != 36 || !cyc) return -1;
         run_cert36(in, moves, out, lens, status, n);
+        return 0;
+    }
+    if (variant == 5 || variant == 6) {  // class-split certified step; 6 = padding filled with 0xFF instead of 0
+        if (m != 36 || !cyc) return -1;
+        run_cert36_split(in, moves, out, lens, status, n, variant == 6 ? 0xFF : 0x00);
         return 0;
     }
     if (variant == 2) {

@@ -67,7 +67,8 @@ def test_host_certified_rows(oracle, golden_dir):
     for rep in range(3):
         mv = rng.integers(0, 12, len(rows)).astype(np.uint8)
         eo, el, es = oracle.acmove_batch(rows, mv, cyclical=1, threads=4)
-        o, l, st = harness.move_batch(rows, mv, 1, 4, 1)
-        assert np.array_equal(o, eo)
-        assert np.array_equal(l.astype(np.int32), el)
-        assert np.array_equal(st, es)
+        for variant in (4, 5, 6):  # plane path; class-split byte/plane path with 0x00 / 0xFF in the stage padding
+            o, l, st = harness.move_batch(rows, mv, 1, variant, 1)
+            assert np.array_equal(o, eo)
+            assert np.array_equal(l.astype(np.int32), el)
+            assert np.array_equal(st, es)
