@@ -68,7 +68,7 @@ class EnvIO(ctypes.Structure):
     """acx_env_io of include/acx.h (field for field)"""
 
     _fields_ = [
-        ("state", _PTR), ("meta", _PTR), ("actions", _PTR), ("step_out", _PTR), ("reward_clipped", _PTR),
+        ("state", _PTR), ("state_out", _PTR), ("meta", _PTR), ("actions", _PTR), ("step_out", _PTR), ("reward_clipped", _PTR),
         ("row_status", _PTR), ("err_count", _PTR), ("pool", _PTR), ("next_idx", _PTR), ("action_ring", _PTR),
         ("t", _I64), ("ring_len", ctypes.c_int32), ("fin_cap", ctypes.c_int32), ("fin_count", _PTR), ("fin_env", _PTR),
         ("fin_steps", _PTR), ("fin_state", _PTR), ("chain", _PTR), ("n", _I64), ("m", ctypes.c_int32),

@@ -155,13 +155,21 @@ class EnvBuffers:
             self.certified = False  # an arbitrary starting state: back to the checked kernel
 
 
-def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0), chained=False):
+def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0), chained=False, state_in=None, state_out=None, rec_out=None):
     """ACEnv.step over all envs in place (ac_env.py:91-111) + reset of finished envs from buf.pool.
 
     chained=True promises that `actions` (and next_idx) were complete before the previous env_step on this buffer
     was launched and that nothing else wrote its state in between: consecutive steps then overlap head-to-tail
-    (acx.h: ACX_ENV_CHAINED)."""
+    (acx.h: ACX_ENV_CHAINED).
+
+    state_in / state_out / rec_out (int8 [N,2m], int8 [N,2m], uint8 [N,8]) redirect the rows read, the rows written and
+    the step records, e.g. to rows t, t+1 of a rollout buffer: the step then needs no observation copy.  The caller
+    keeps track of where the current states are (buf.state is not rebound)."""
     _chk(actions, torch.uint8, (buf.n,), "actions")
+    for t, shape, name in ((state_in, buf.state.shape, "state_in"), (state_out, buf.state.shape, "state_out"),
+                           (rec_out, buf.step_out.shape, "rec_out")):
+        if t is not None:
+            _chk(t, buf.state.dtype if name != "rec_out" else torch.uint8, shape, name)
     stream = _prep(buf.state.device)
     pool = buf.pool if next_idx is not None else None
     if next_idx is not None:
@@ -169,7 +177,10 @@ def env_step(buf, actions, next_idx=None, clip=(-10.0, 1000.0), chained=False):
         if pool is None:
             raise ValueError("next_idx given but the env buffers hold no pool")
     io = _lib.EnvIO()
-    io.state, io.meta, io.actions, io.step_out = _ptr(buf.state), _ptr(buf.meta), _ptr(actions), _ptr(buf.step_out)
+    io.state = _ptr(buf.state if state_in is None else state_in)
+    io.state_out = _ptr(state_out)
+    io.meta, io.actions = _ptr(buf.meta), _ptr(actions)
+    io.step_out = _ptr(buf.step_out if rec_out is None else rec_out)
     io.reward_clipped, io.row_status, io.err_count = _ptr(buf.reward_clipped), _ptr(buf.status), _ptr(buf.err_count)
     io.pool, io.next_idx = _ptr(pool), _ptr(next_idx)
     io.action_ring, io.t, io.ring_len = _ptr(buf.ring), buf.t, buf.horizon

@@ -420,7 +420,7 @@ class ShardedBFS:
         self.chunk = int(chunk)
         self.dev = shard.dev
         self.n_nodes, self.n_expanded, self.levels = 1, 0, []
-        self.comm_bytes, self.rounds = 0, 0
+        self.comm_bytes, self.rounds, self.n_candidates = 0, 0, 0
         # pipeline=True stages round k + 1 on a side stream while round k is probed and committed.  Measured on 8 B200:
         # no gain (the NVLink-bound staging kernel and the latency-bound probe slow each other down), so it is off.
         self.pipeline, self.stage_ctas = bool(pipeline), int(stage_ctas)
@@ -456,6 +456,7 @@ class ShardedBFS:
         if any(row[G] for row in allc):
             raise RuntimeError("sharded bfs: a send region overflowed (hash imbalance above the 15% head room)")
         self.shard.deliver(allc, k)
+        self.n_candidates += sum(allc[self.rank][:G])  # records this rank staged (children that differ from their parent)
         return self.shard.rec * (sum(allc[self.rank][:G]) - allc[self.rank][self.rank])
 
     def _lookup(self, gid):

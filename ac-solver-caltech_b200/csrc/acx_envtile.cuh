@@ -26,7 +26,8 @@
 namespace acx {
 
 struct EnvParams {
-    int8_t* state;
+    int8_t* state;      // rows are read from here ...
+    int8_t* state_out;  // ... and written here (== state: in place)
     uint32_t* meta;
     const uint8_t* actions;
     uint8_t* step_out;
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(TR) k_env_tiles(const EnvParams p, int64_t nti
         if (tid == 0) {
             const uint32_t base = stage0 + s * L::STAGE;
             const int64_t g = tile0 + t;
-            bulk_store(p.state + g * L::STATE, base, L::STATE);
+            bulk_store(p.state_out + g * L::STATE, base, L::STATE);
             bulk_store(reinterpret_cast<uint8_t*>(p.meta) + g * L::META, base + L::OFF_META, L::META);
             bulk_store(p.step_out + g * L::REC, base + L::OFF_REC, L::REC);
             if (p.reward_clipped) bulk_store(reinterpret_cast<uint8_t*>(p.reward_clipped) + g * L::CLIP, base + L::OFF_CLIP, L::CLIP);

@@ -282,7 +282,11 @@ static int launch_env_tiles(EnvParams e, int64_t ntiles, bool whole_batch, cudaS
         ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TR, smem));
         ctas_per_sm[dev] = occ > 0 ? occ : 1;
     }
-    const int64_t grid = std::min<int64_t>(ntiles, (int64_t)sm_count() * ctas_per_sm[dev]);
+    // every CTA gets the same number of tiles (+-1): with 8192 tiles on 1332 resident CTAs, 15 % of the CTAs would
+    // otherwise run a 7th tile alone at the end of the launch
+    const int64_t resident = (int64_t)sm_count() * ctas_per_sm[dev];
+    const int64_t per_cta = (ntiles + resident - 1) / resident;
+    const int64_t grid = (ntiles + per_cta - 1) / per_cta;
     // the per-CTA dependency replaces the grid-wide one only when this launch is the whole step
     if (grid > ACX_ENV_CHAIN_SLOTS) e.chain = nullptr;
     if (!e.chain || !whole_batch || !pdl_enabled()) e.chain_wait = 0;
@@ -327,7 +331,7 @@ static int env_stages() {  // ACX_ENV_STAGES=2|3|4 (tuning knob)
 }
 
 static bool env_tiles_usable(const EnvParams& e) {
-    uintptr_t a = (uintptr_t)e.state | (uintptr_t)e.meta | (uintptr_t)e.actions | (uintptr_t)e.step_out |
+    uintptr_t a = (uintptr_t)e.state | (uintptr_t)e.state_out | (uintptr_t)e.meta | (uintptr_t)e.actions | (uintptr_t)e.step_out |
                   (uintptr_t)e.reward_clipped | (uintptr_t)e.status | (uintptr_t)e.ring_row;
     return (a & 15u) == 0;
 }
@@ -454,7 +458,7 @@ extern "C" int acx_env_step(const acx_env_io* io, acx_stream_t stream) {
     StepParams p;
     memset(&p, 0, sizeof p);
     p.in = io->state;
-    p.out = io->state;
+    p.out = io->state_out ? io->state_out : io->state;
     p.actions = io->actions;
     p.status = io->row_status;
     p.n = n;
@@ -462,6 +466,7 @@ extern "C" int acx_env_step(const acx_env_io* io, acx_stream_t stream) {
     p.cyclical = 1;
     EnvParams& e = p.env;
     e.state = io->state;
+    e.state_out = io->state_out ? io->state_out : io->state;
     e.meta = io->meta;
     e.actions = io->actions;
     e.step_out = io->step_out;

@@ -31,11 +31,11 @@ M = 36
 N_ENV = 1 << 20
 HORIZON = 2000
 N_BATCHES = 4  # rotating resident batches: 4 x 75.5 MB of state > 126 MB L2
-# 89.28 MB read + 35.09 MB written per launch of 2^20 envs (ncu --set full capture, end of round 1)
-NCU_DRAM_BYTES_PER_LAUNCH = 124.4e6
 ALG_BYTES = 4 * M + 9  # read state 2m + action 1; write state 2m + lens 2 + reward 4 + done 1 + trunc 1
 METRIC = "AC-move transitions/sec (lockstep ACEnv.step)"
 UNIT = "transitions/s"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the env kernel, from the committed ncu capture
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r02_env_step_dram_traffic.json")
 
 
 def parse_args():
@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument("--envs", type=int, default=N_ENV)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of one CUDA graph")
+    ap.add_argument("--no-bfs", action="store_true", help="skip the hash-partitioned bfs leg (configs[3])")
+    ap.add_argument("--no-other", action="store_true", help="skip configs[0], [2], [4] (one GPU only)")
+    ap.add_argument("--bfs-budget", type=float, default=1e9)
     return ap.parse_args()
 
 
@@ -59,6 +62,7 @@ def config_dict(n_env, n_gpus):
         "l2": "rotating %d resident batches (%.0f MB of state per GPU) > 126 MB L2; no flush needed"
               % (N_BATCHES, N_BATCHES * n_env * 2 * M / 1e6),
         "sharding": "env batches sharded across %d GPU(s), no communication" % n_gpus,
+        "reference_arm_envs": n_env,
     }
 
 
@@ -178,7 +182,7 @@ def reference_arm(args):
     cores = os.cpu_count() or 1
     pool = load_pool()
     rng = np.random.default_rng(0)
-    n = min(args.envs, 1 << 18)
+    n = args.envs  # the GPU arm's env count
     state = pool[rng.integers(0, len(pool), n)].copy()
     steps = np.zeros(n, dtype=np.int32)
     nxt = rng.integers(0, len(pool), n).astype(np.int32)
@@ -205,6 +209,51 @@ def reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------------
+def _time_steps(step, n_steps, warm0, dev, barrier, use_graph):
+    """K launches timed with CUDA events on the launching stream; with use_graph the K launches are ONE CUDA graph
+    (same kernels, same order, same buffers).  Returns (milliseconds, wall-clock start of the timed region)."""
+    import torch
+
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    graph = None
+    if use_graph:
+        graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(graph, stream=side):
+                for k in range(n_steps):
+                    step(warm0 + k)
+        torch.cuda.current_stream(dev).wait_stream(side)
+    barrier()
+    t_wall0 = time.time()
+    e0.record()
+    if graph is not None:
+        graph.replay()
+    else:
+        for k in range(n_steps):
+            step(warm0 + k)
+    e1.record()
+    barrier()
+    return e0.elapsed_time(e1), t_wall0
+
+
+def other_configs(dev):
+    """configs[0], [2], [4] in the driver-run line (one GPU): same event discipline, a few seconds each"""
+    import bench_configs as C
+
+    out = {}
+    g = C.cfg_greedy(dev)
+    out["greedy_1190"] = {"config": g["config"], "wall_s": g["wall_s"], "solved": g["solved"], "expected_solved": 380,
+                          "nodes_expanded_per_s": g["nodes_expanded_per_s"], "reference": g["reference"]}
+    for key, kw in (("expand12_m128", dict(m=128, chunk=1 << 19, total=1 << 25)), ("expand12_m36", dict(m=36, chunk=1 << 20, total=1 << 26))):
+        e = C.cfg_expand(dev, **kw)
+        out[key] = {"config": e["config"].replace("1e8-state", "%d-state" % e["parents"]), "parents_per_s": e["parents_per_s"],
+                    "transitions_per_s": e["transitions_per_s"], "frac": e["roofline"]["frac"], "alg_bytes_per_parent": e["alg_bytes_per_parent"]}
+    out["ppo_rollout"] = C.cfg_ppo(dev)
+    return out
+
+
 def gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -219,8 +268,16 @@ def gpu_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
+        # the communicator's own "rank r nranks N" lines go to stderr; stdout stays the one JSON line
+        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
+        probe = torch.ones(1, device=dev)
+        dist.all_reduce(probe)
+        if rank == 0:
+            sys.stderr.write("bench.py: NCCL communicator up: world_size %d, all_reduce(1) = %d, NCCL %s\n"
+                             % (dist.get_world_size(), int(probe.item()), ".".join(map(str, torch.cuda.nccl.version()))))
 
     n = args.envs
     pool_np = load_pool()
@@ -230,52 +287,47 @@ def gpu_arm(args):
     bufs, acts, nxts = [], [], []
     for b in range(N_BATCHES):
         states = walk_states_gpu(pool, n, seed=100 * rank + b, dev=dev)
+        # the timed step writes the 8-byte record only (reward, done, truncated, lengths); the clipped float reward and
+        # the per-row status are optional outputs of the same kernel, used by the e2e leg below
         bufs.append(batch.EnvBuffers(states, HORIZON, pool=pool, want_clip=False, want_status=False))
         assert bufs[-1].certified, "bench states must be certified rows"
         bufs[-1].set_steps(torch.randint(0, HORIZON, (n,), device=dev, generator=g, dtype=torch.int32))
         acts.append(torch.randint(0, 12, (n,), device=dev, generator=g, dtype=torch.int64).to(torch.uint8))
         nxts.append(torch.randint(0, pool.shape[0], (n,), device=dev, generator=g, dtype=torch.int32))
-    before = bufs[0].state.clone()
 
-    chained = os.environ.get("ACX_BENCH_CHAINED", "1") != "0"
-
-    def step(k):
-        b = k % N_BATCHES
-        batch.env_step(bufs[b], acts[(k // N_BATCHES) % N_BATCHES], next_idx=nxts[b], chained=chained)
+    def make_step(chained):
+        def step(k):
+            b = k % N_BATCHES
+            batch.env_step(bufs[b], acts[(k // N_BATCHES) % N_BATCHES], next_idx=nxts[b], chained=chained)
+        return step
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    # the actions of every step exist before the first launch and nothing else touches the env buffers between two
+    # steps, so consecutive launches may be chained (per-CTA row dependency instead of the grid-wide one, acx.h)
+    chained = os.environ.get("ACX_BENCH_CHAINED", "1") != "0"
+    step = make_step(chained)
+    # fraction of rows ONE step leaves unchanged (guard rejection, a conjugation that reduces back to the same word) on
+    # the distribution the timed steps see: a scratch copy of batch 0 takes one step (61 % on uniform walks)
+    scratch = batch.EnvBuffers(bufs[0].state.clone(), HORIZON, pool=pool, want_clip=False, want_status=False)
+    scratch.set_steps(bufs[0].steps)
+    before = scratch.state.clone()
+    batch.env_step(scratch, acts[0], next_idx=nxts[0])
+    torch.cuda.synchronize()
+    noop = float((scratch.state == before).all(dim=1).float().mean().item())
+    finished = float((scratch.done.bool() | scratch.truncated.bool()).float().mean().item())
+    mean_total_len = float(scratch.lens.sum(dim=1).float().mean().item())
+    del scratch, before
     for k in range(args.warmup):
         step(k)
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_wall0 = time.time()
-    graph = None
-    if not args.no_graph:  # the K timed launches as ONE CUDA graph (same kernels, same order, same buffers)
-        graph = torch.cuda.CUDAGraph()
-        side = torch.cuda.Stream(dev)
-        side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):
-            with torch.cuda.graph(graph, stream=side):
-                for k in range(args.steps):
-                    step(args.warmup + k)
-        torch.cuda.current_stream(dev).wait_stream(side)
-        barrier()
-        t_wall0 = time.time()
-    e0.record()
-    if graph is not None:
-        graph.replay()
-    else:
-        for k in range(args.steps):
-            step(args.warmup + k)
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    ms, t_wall0 = _time_steps(step, args.steps, args.warmup, dev, barrier, not args.no_graph)
+    ms_unchained, _ = _time_steps(make_step(False), args.steps, args.warmup + args.steps, dev, barrier, not args.no_graph)
     # keep the same kernel running ~1.2 s more (untimed) so that nvidia-smi sees the clocks under this load
     t_hold = time.time()
     k = 0
@@ -285,10 +337,9 @@ def gpu_arm(args):
             k += 1
         torch.cuda.synchronize()
     clocks = sampler.stop(t_wall0, time.time())
-    changed = float((bufs[0].state != before).any(dim=1).float().mean().item())
 
     # end to end through the host-buffer API (VecACEnv.step: numpy actions in, numpy results out)
-    env = vecenv.VecACEnv(pool_np, horizon_length=HORIZON, num_envs=n, device=str(dev),
+    env = vecenv.VecACEnv(pool_np, horizon_length=HORIZON, num_envs=n, device=str(dev), track_actions=False,
                           start_index=np.random.default_rng(rank).integers(0, len(pool_np), n))
     env.reset()
     env.buf.set_state(bufs[1].state)
@@ -303,17 +354,13 @@ def gpu_arm(args):
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
 
-    tm = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+    tm = torch.tensor([ms, e2e_s * 1e3, ms_unchained], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = float(tm[0]), float(tm[1])
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+    ms, e2e_ms, ms_unchained = float(tm[0]), float(tm[1]), float(tm[2])
+    del bufs, acts, nxts, env
+    torch.cuda.empty_cache()
 
-    value = world * n * args.steps / (ms * 1e-3)
-    kern_s = ms * 1e-3 / args.steps  # one launch per step
     peaks = {}
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -321,26 +368,65 @@ def gpu_arm(args):
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+
+    bfs = None
+    if not args.no_bfs:
+        import bench_bfs
+
+        if world == 1:
+            bench_bfs.init_single_process_group(dev)
+        bfs = bench_bfs.bfs_leg(dev, int(args.bfs_budget), peak_gbs=peak)
+    others = None
+    if world == 1 and not args.no_other and rank == 0:
+        others = other_configs(dev)
+    if rank != 0:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+        return
+
+    value = world * n * args.steps / (ms * 1e-3)
+    kern_s = ms * 1e-3 / args.steps  # one launch per step
     achieved = n * ALG_BYTES / kern_s / 1e9
+    traffic, traffic_src = None, "no capture committed"
+    try:
+        with open(TRAFFIC_FILE) as f:
+            tr = json.load(f)
+        if n == tr.get("envs"):
+            traffic, traffic_src = tr["dram_bytes_per_launch"], tr["source"]
+    except (OSError, ValueError, KeyError):
+        pass
+    e2e_value = world * n * e2e_steps / (e2e_ms * 1e-3)
+    d2h = n * 2 * M + 4 * n + 8 * n + 8
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "i8", "data": "synthetic", "config": config_dict(n, world),
         "clocks": clocks,
-        "e2e": {"value": world * n * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT,
-                "h2d_bytes_per_step": env.h2d_bytes_per_step, "d2h_bytes_per_step": env.d2h_bytes_per_step,
-                "api": "acx.vecenv.VecACEnv.step(numpy actions) -> numpy obs/reward/done/truncated", "steps": e2e_steps},
-        "gpu_launches": args.steps, "launch_mode": "python loop" if args.no_graph else "one CUDA graph of the K launches",
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n, "d2h_bytes_per_step": d2h,
+                "api": "acx.vecenv.VecACEnv.step(numpy actions) -> numpy obs/reward/done/truncated/infos", "steps": e2e_steps,
+                "bound": "pcie", "d2h_gbs_per_gpu": d2h / (e2e_ms * 1e-3 / e2e_steps) / 1e9,
+                "note": "72 B of int8 observation per env per step cross PCIe (a host-side consumer cannot avoid them); the "
+                        "kernel is 1-2 % of the step"},
+        "gpu_launches": args.steps,
+        "launch_mode": ("python loop" if args.no_graph else "one CUDA graph of the K launches") +
+                       ("; consecutive steps chained by per-CTA row dependencies (ACX_ENV_CHAINED)" if chained else ""),
+        "unchained": {"value": world * n * args.steps / (ms_unchained * 1e-3), "ms_per_step": ms_unchained / args.steps,
+                      "frac": n * ALG_BYTES / (ms_unchained * 1e-3 / args.steps) / 1e9 / peak,
+                      "note": "same launches ordered grid-after-grid (griddepcontrol.wait): what a step costs when its actions are "
+                              "produced by the kernel launched just before it"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": NCU_DRAM_BYTES_PER_LAUNCH if n == (1 << 20) else None,
-                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full of this command "
-                                       "(profiles/r01_k_rows_tma_env_m36_ncu_full_summary.txt); below the algorithmic "
-                                       "bytes because the last stores of a 40 us kernel still sit in the 126 MB L2",
-                     "alg_bytes_per_launch": n * ALG_BYTES, "kernel": "k_rows_tma<W=2,MS=36,TR=128,S=3,ENV,CERT>",
+                     "traffic": traffic, "traffic_source": traffic_src,
+                     "alg_bytes_per_launch": n * ALG_BYTES, "kernel": "k_env_tiles<MS=36,TR=128,S>",
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
                      "alg_bytes_per_transition": ALG_BYTES},
-        "changed_row_fraction": changed,
+        "noop_row_fraction_per_step": noop, "finished_env_fraction_per_step": finished, "mean_total_length": mean_total_len,
     }
+    if bfs is not None:
+        line["bfs"] = bfs
+    if others is not None:
+        line["other_configs"] = others
+    if world > 1:
+        line["nccl"] = {"world_size": dist.get_world_size(), "version": ".".join(map(str, torch.cuda.nccl.version()))}
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         v, sample = cpu_oracle_throughput(n, 10.0 / max(1, cores) + 2.0, cores)
@@ -348,7 +434,7 @@ def gpu_arm(args):
                                 "sample": sample + " (C oracle, %d pthreads; the reference itself is pure Python, "
                                                    "about 1e4 ACMove/s/core)" % cores}
     print(json.dumps(line))
-    if world > 1:
+    if dist.is_initialized():
         dist.destroy_process_group()
 
 

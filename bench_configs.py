@@ -105,52 +105,79 @@ def cfg_expand(dev, m=128, chunk=1 << 19, total=10 ** 8):
 
 
 def cfg_ppo(dev, n=65536, T=64):
-    """configs[2]: PPO rollout with 65,536 GPU-resident envs: the reference Agent's 2x256 tanh MLP samples the
-    actions on the same GPU (agents/ppo_agent.py:52-109), no host hop per step."""
+    """configs[2]: PPO rollout with 65,536 GPU-resident envs.  The rollout of agents/training.py:229-241 as ONE CUDA
+    graph of T steps: step t reads the observations from row t of the rollout buffer and writes row t+1 and the step
+    record of row t (acx_env_io.state_out / step_out), so the env side of a step is exactly one kernel and no copy.
+    env_only: pre-sampled actions, steps chained.  with_policy: the reference Agent's 2x256 tanh actor / critic
+    (agents/ppo_agent.py:52-109) sample the actions on the same GPU inside the same graph."""
     from acx import vecenv
 
     pool = B.load_pool()
-    env = vecenv.VecACEnv(pool, horizon_length=2000, num_envs=n, device=str(dev))
+    env = vecenv.VecACEnv(pool, horizon_length=2000, num_envs=n, device=str(dev), track_actions=False)
     env.reset()
+    buf = env.buf
     torch.manual_seed(0)
     actor = torch.nn.Sequential(torch.nn.Linear(72, 256), torch.nn.Tanh(), torch.nn.Linear(256, 256), torch.nn.Tanh(),
                                 torch.nn.Linear(256, 12)).to(dev)
     critic = torch.nn.Sequential(torch.nn.Linear(72, 256), torch.nn.Tanh(), torch.nn.Linear(256, 256), torch.nn.Tanh(),
                                  torch.nn.Linear(256, 1)).to(dev)
-    obs_buf = torch.zeros((T, n, 72), dtype=torch.int8, device=dev)
-    act_buf = torch.zeros((T, n), dtype=torch.uint8, device=dev)
-    rew_buf = torch.zeros((T, n), dtype=torch.float32, device=dev)
-    done_buf = torch.zeros((T, n), dtype=torch.uint8, device=dev)
+    obs_buf = torch.zeros((T + 1, n, 72), dtype=torch.int8, device=dev)
+    rec_buf = torch.zeros((T, n, 8), dtype=torch.uint8, device=dev)  # reward | done | truncated | lengths per step
+    act_buf = torch.randint(0, 12, (T, n), device=dev, dtype=torch.int64).to(torch.uint8)
     val_buf = torch.zeros((T, n), dtype=torch.float32, device=dev)
+    logp_buf = torch.zeros((T, n), dtype=torch.float32, device=dev)
+    obs_buf[0].copy_(buf.state)
 
     def rollout(with_policy):
         for t in range(T):
-            obs = env.buf.state
-            obs_buf[t].copy_(obs)
             if with_policy:
                 with torch.no_grad():
-                    x = obs.float()
+                    x = obs_buf[t].float()
                     logits = actor(x)
                     val_buf[t].copy_(critic(x).squeeze(-1))
-                    a = torch.distributions.Categorical(logits=logits).sample().to(torch.uint8)
-            else:
-                a = act_buf[(t + 1) % T]
-            act_buf[t].copy_(a)
-            _, r, d, tr = env.step_device(act_buf[t])
-            rew_buf[t].copy_(r)
-            done_buf[t].copy_(d | tr)
+                    logp = torch.log_softmax(logits, dim=-1)
+                    a = torch.multinomial(logp.exp(), 1).squeeze(-1)
+                    logp_buf[t].copy_(logp.gather(1, a[:, None]).squeeze(-1))
+                    act_buf[t].copy_(a)
+            batch.env_step(buf, act_buf[t], next_idx=env.next_state_index, clip=env.clip, chained=not with_policy,
+                           state_in=obs_buf[t], state_out=obs_buf[t + 1], rec_out=rec_buf[t])
+        obs_buf[0].copy_(obs_buf[T])
 
     out = {}
-    for with_policy in (True, False):
-        rollout(with_policy)
+    for with_policy in (False, True):
+        key = "with_policy" if with_policy else "env_only"
+        rollout(with_policy)  # warm-up, eager
+        torch.cuda.synchronize()
+        graph, mode = None, "eager"
+        try:
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(g, stream=side):
+                    rollout(with_policy)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            graph, mode = g, "one CUDA graph per rollout of %d steps" % T
+        except Exception as ex:  # capture of the sampling ops is a torch matter: fall back to eager launches
+            mode = "eager (graph capture failed: %s)" % type(ex).__name__
+            torch.cuda.synchronize()
+        reps = 5
+        (graph.replay if graph is not None else (lambda: rollout(with_policy)))()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(3):
-            rollout(with_policy)
+        for _ in range(reps):
+            if graph is not None:
+                graph.replay()
+            else:
+                rollout(with_policy)
         e1.record()
         torch.cuda.synchronize()
-        out["env_steps_per_s_%s" % ("with_policy" if with_policy else "env_only")] = 3 * T * n / (e0.elapsed_time(e1) * 1e-3)
+        ms = e0.elapsed_time(e1)
+        out["env_steps_per_s_" + key] = reps * T * n / (ms * 1e-3)
+        out["us_per_step_" + key] = 1e3 * ms / (reps * T)
+        out["launch_mode_" + key] = mode
+    assert int(buf.err_count.item()) == 0
     out.update({"config": "configs[2] PPO rollout, %d GPU-resident envs per B200, %d steps per rollout" % (n, T),
                 "reference": "627 env-steps/s end to end with 4 envs (experiments/results/2026-02-23_03-11-29_ppo_rnd/results.json)"})
     return out
@@ -258,4 +285,5 @@ if __name__ == "__main__":
                 print(json.dumps(line))
         elif w == "bfs":
             import bench_bfs
-            print(json.dumps(bench_bfs.run(dev)))
+            bench_bfs.init_single_process_group(dev)
+            print(json.dumps(bench_bfs.bfs_leg(dev, 10 ** 7)))

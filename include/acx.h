@@ -110,7 +110,9 @@ int acx_rows_primitive(const int8_t* states_in, const uint8_t* moves, int8_t* st
 #define ACX_ENV_CHAINED 2
 #define ACX_ENV_CHAIN_SLOTS 4096
 typedef struct acx_env_io {
-    int8_t* state;           /* [n, 2m] in place */
+    int8_t* state;           /* [n, 2m] current states (rewritten in place when state_out is NULL) */
+    int8_t* state_out;       /* [n, 2m] or NULL: write the next states here instead and leave `state` untouched
+                                (e.g. row t+1 of a rollout buffer whose row t is `state`: no observation copy) */
     uint32_t* meta;          /* [n] in place */
     const uint8_t* actions;  /* [n] move ids 0..11 */
     uint8_t* step_out;       /* [n, 8] */
