@@ -103,7 +103,7 @@ class GpuShard:
         self.world, self.rank = G, rank
         self.fused = self._fusable(G)
         f = self.fmax
-        self.rcap = 12 * f if G == 1 else min(12 * f, int(12 * f / G * 1.15) + 8192)
+        self.rcap = self._region_cap(G, f)
         if self.transport == "auto":
             self.transport = "p2p" if (self.fused and G > 1) else "nccl"
         if self.transport == "p2p" and not (self.fused and G > 1):
@@ -146,6 +146,10 @@ class GpuShard:
 
     def _fusable(self, world):
         return self.m == 36 and world <= 32
+
+    def _region_cap(self, G, f):
+        """records one sender may put into one owner's region per round: all 12 f for one rank, else the mean plus 15 %"""
+        return 12 * f if G == 1 else min(12 * f, int(12 * f / G * 1.15) + 8192)
 
     def node_total(self, k):
         return self.total[k].to(torch.int64)

@@ -31,6 +31,15 @@ def _make_engine(root, budget, cyclical, world, dev, chunk, prof=False):
     cap_local = int(budget / world * (1.0 if world == 1 else 1.06)) + 4096
     max_parents = chunk if world == 1 else min(chunk, int(chunk / world * 1.15) + 8192)
     transport = os.environ.get("ACX_BFS_TRANSPORT", "auto")
+    if os.environ.get("ACX_BFS_ENGINE", "v2") == "v2":  # device-driven rounds (acx/pbfs.py)
+        from acx.pbfs import PlaneBFS, make_plane_shard
+
+        shard = make_plane_shard(root, cyclical, cap_local, max_parents, str(dev), transport=transport)
+        if shard is not None:
+            eng = PlaneBFS(root, budget, shard, chunk=chunk)
+            if prof:
+                eng.timers = {}
+            return eng, shard
     if os.environ.get("ACX_BFS_NODES", "planes") == "bytes":
         shard = GpuShard(len(root) // 2, cyclical, cap_local, max_parents, str(dev), transport=transport)
     else:
@@ -64,7 +73,7 @@ def _timed_run(root, budget, cyclical, world, dev, chunk, prof=False):
         phases = {k: round(1e3 * float(v), 3) for k, v in zip(keys, ph)}
     out = {"solved": ok, "path": path, "n_seen": eng.n_nodes, "nodes_expanded": eng.n_expanded, "wall_s": float(dt[0]),
            "levels": list(eng.levels), "rounds": eng.rounds, "sent_bytes": int(sent[0]), "candidates": int(sent[1]),
-           "transport": shard.transport, "nodes": type(shard).__name__, "phase_ms": phases}
+           "transport": shard.transport, "nodes": type(shard).__name__, "engine": type(eng).__name__, "phase_ms": phases}
     shard.close()
     del eng, shard
     torch.cuda.empty_cache()
@@ -126,7 +135,7 @@ def bfs_leg(dev, budget=10 ** 9, chunk_per_rank=1 << 20, large=True, peak_gbs=65
                   "cyclically_reduce_after_moves=False, max_nodes_to_explore=%d, visited set hash-partitioned over %d GPU(s)" % (budget, world),
         "nodes_expanded_per_s": exp / dt, "discovered_per_s": seen / dt, "wall_s": dt, "n_seen": seen, "nodes_expanded": exp,
         "solved": best["solved"], "levels": best["levels"], "rounds": best["rounds"], "budget": budget, "scaling": "strong",
-        "chunk_parents_per_round": chunk, "transport": best["transport"], "nodes": best["nodes"],
+        "chunk_parents_per_round": chunk, "transport": best["transport"], "nodes": best["nodes"], "engine": best["engine"],
         "candidates": best["candidates"], "all_to_all_bytes_total": best["sent_bytes"],
         "nvlink_egress_gbs_per_rank": best["sent_bytes"] / world / dt / 1e9,
         "phase_ms": prof["phase_ms"], "phase_ms_note": "max over ranks, from a separate run with a device sync per phase (%.1f ms in all)" % (1e3 * prof["wall_s"]),

@@ -250,6 +250,39 @@ int acx_pbfs_commit(const uint64_t* recs, const int64_t* region_counts, int n_re
                     int64_t gid_base, uint64_t* n_local, uint64_t* table, uint64_t* nodes, int64_t* gid, int64_t* parent,
                     uint8_t* action, acx_stream_t stream);
 
+/* The device-driven round of the plane bfs (csrc/acx_pbfs2.cu; driver acx/pbfs.py): same records, table and search
+ * semantics as above, but nothing comes back to the host inside a level.  `ctl` is a control block of int64 words in
+ * device memory, identical on every rank: [0] stop code (0 none, 1 solved, 2 error, 3 budget), [1] len(tree_nodes),
+ * [2] nodes expanded, [3] first global id of the round being committed, [4] order of the deciding candidate
+ * (parent * 12 + action inside the round), [5] global id of the round's first parent, [6] a region overflowed, [7] rounds,
+ * [8] records this rank staged, [9] of which for itself (at least 10 words); every kernel returns at once when ctl[0] != 0.
+ * counts = the all-gathered cursors, int64 [world, world + 1]: counts[s][o] records rank s staged for owner o, counts[s][world]
+ * its overflow flag; the regions a rank received hold region_counts_dev[s * count_stride] records (= counts[s][rank]).
+ *   acx_pbfs_expand2  as acx_pbfs_expand, plus: the records of a CTA are sorted by owner in shared memory and written as
+ *                     contiguous runs padded to 4 records (128 bytes) with null records (region_cap % 4 == 0, regions
+ *                     128-byte aligned); with cyclical == 0 the child that undoes the move `action[parent]` (the
+ *                     grandparent; 255 = no such move) is not sent.  cursor[o] counts records incl. padding.
+ *   acx_pbfs_probe2   region counts are a DEVICE array; the winner resolution is fused in: mask32 (uint32 view of one
+ *                     uint16 per parent, caller zeroes) has bit a of parent p set iff child (p, a) is the first discovery
+ *                     of a new state, slot[j] >= 0 exactly for those candidates; mins = {min success order, min error
+ *                     order} (caller sets both to 2^62).
+ *   acx_pbfs_decide   exclusive scan of popcount(mask16) -> excl_out (int32), then the decision of the round
+ *                     (breadth_first.py:84-95 in the reference's order) into ctl.  temp == NULL returns the scratch size.
+ *   acx_pbfs_commit2  claim holders become nodes with global id ctl[3] + excl[p] + popcount(mask16[p] & bits below a). */
+int acx_pbfs_expand2(const uint64_t* nodes, const uint8_t* action, const int64_t* loc, const int64_t* gids, int64_t ord_base,
+                     int64_t f, int m, int cyclical, int world, int64_t region_cap, uint64_t* cursor,
+                     uint8_t* const* dst_regions, const int64_t* ctl, acx_stream_t stream);
+int acx_pbfs_probe2(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap, uint64_t* table,
+                    int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins, uint32_t* mask32, const int64_t* ctl,
+                    acx_stream_t stream);
+int64_t acx_pbfs_decide(const uint16_t* mask16, int32_t* excl_out, int64_t n_parents, const uint64_t* mins, int64_t parent_base,
+                        int64_t budget, int64_t* ctl, const int64_t* counts, int world, int rank, void* temp, int64_t temp_bytes,
+                        acx_stream_t stream);
+int acx_pbfs_commit2(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap,
+                     const int64_t* slot, const int32_t* excl, const uint32_t* mask32, int64_t parent_base, const int64_t* ctl,
+                     uint64_t* n_local, uint64_t* table, uint64_t* nodes, int64_t* gid, int64_t* parent, uint8_t* action,
+                     acx_stream_t stream);
+
 /* Exclusive scan of popcount(mask[p]) over the parents of a round: excl_out[p] = new nodes discovered by the
  * parents before p (reference order), total_out[0] = new nodes of the round.  temp == NULL returns the scratch
  * size in bytes; otherwise 0 / a negative error. */

@@ -137,3 +137,43 @@ def test_plane_nodes_pack_expand_unpack(cuda, oracle, golden_dir):
         assert (status == st[order]).all()
         same = (ch == np.repeat(rows_ok, 12, axis=0)).all(axis=1) & (st == 0)
         assert (seen == ~same).all()  # exactly the children that differ from their parent (or raise) are sent
+
+
+def test_plane_bfs_device_driven_single_rank(cuda, oracle, golden_dir):
+    """acx.pbfs.PlaneBFS (device-driven rounds, owner-sorted line-sized runs, fused winner resolution, grandparent
+    filter, on-device budget / success decision) against the oracle: (solved, path, len(tree_nodes), expanded) for small
+    and large budgets, several chunk sizes, both reduction modes, solved and budget-cut exits"""
+    import torch.distributed as dist
+
+    from acx.pbfs import PlaneBFS, make_plane_shard
+    from helpers import AK2, AK3, pad_row, repad
+
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", str(29700 + os.getpid() % 200))
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=cuda)
+    try:
+        rows = dataset_rows(golden_dir)
+        rng = np.random.default_rng(33)
+        cases = [(repad(AK2, 8), 4000, False, 64), (repad(AK2, 8), 4000, False, 1 << 16), (pad_row(*AK3, 36), 200000, False, 4096),
+                 (pad_row(*AK3, 36), 50000, True, 100000), (pad_row(*AK3, 36), 1500000, False, 1 << 18)]
+        for k in rng.choice(len(rows), size=10, replace=False):
+            for budget, chunk in ((1, 4), (13, 4), (14, 4), (700, 64), (30000, 256), (30000, 4096)):
+                cases.append((rows[int(k)], budget, bool(rng.integers(0, 2)), chunk))
+        n_solved = 0
+        for row, budget, cyc, chunk in cases:
+            row = np.asarray(row, dtype=np.int8)
+            stats = {}
+            ook, opath = oracle.bfs(row, budget, False, cyc, stats=stats)
+            shard = make_plane_shard(row, cyc, budget + 64, chunk, str(cuda))
+            assert shard is not None
+            eng = PlaneBFS(row, budget, shard, chunk=chunk)
+            ok, path = eng.run()
+            assert (ok, path) == (ook, opath), (row.tolist(), budget, cyc, chunk)
+            assert eng.n_nodes == stats["n_seen"] and eng.n_expanded == stats["n_expanded"], (budget, cyc, chunk)
+            n_solved += int(ok)
+        assert n_solved >= 1
+    finally:
+        if created:
+            dist.destroy_process_group()

@@ -35,6 +35,17 @@ def _worker(rank, world, port, cases, out):
             ok, path = eng.run()
             shard.close()
             res.append((ok, path, eng.n_nodes, eng.n_expanded, shard.transport))
+        # the device-driven engine (acx.pbfs) on the same case
+        from acx.pbfs import PlaneBFS, make_plane_shard
+
+        shard = make_plane_shard(row, cyc, budget + 64, chunk, str(dev))
+        if shard is None:
+            res.append(None)
+        else:
+            eng = PlaneBFS(row, budget, shard, chunk=chunk)
+            ok, path = eng.run()
+            shard.close()
+            res.append((ok, path, eng.n_nodes, eng.n_expanded, shard.transport))
     out.put((rank, res))
     dist.barrier()
     dist.destroy_process_group()
@@ -78,11 +89,11 @@ def test_sharded_bfs_two_gpus_matches_oracle(cuda, oracle, golden_dir):
         stats = {}
         ok, path = oracle.bfs(np.array(row, dtype=np.int8), budget, False, cyc, stats=stats)
         for rank in (0, 1):
-            for t in range(4):
-                if got[rank][4 * idx + t] is None:
+            for t in range(5):
+                if got[rank][5 * idx + t] is None:
                     continue
-                rok, rpath, n_seen, n_exp, transport = got[rank][4 * idx + t]
+                rok, rpath, n_seen, n_exp, transport = got[rank][5 * idx + t]
                 assert (rok, rpath) == (ok, path), (idx, rank, t, transport)
                 assert n_seen == stats["n_seen"] and n_exp == stats["n_expanded"], (idx, rank, t, transport)
-        assert got[0][4 * idx][4] == ("p2p" if len(row) == 72 else "nccl")
-        assert got[0][4 * idx + 2] is None or got[0][4 * idx + 2][4] == "p2p"
+        assert got[0][5 * idx][4] == ("p2p" if len(row) == 72 else "nccl")
+        assert got[0][5 * idx + 2] is None or got[0][5 * idx + 2][4] == "p2p"
