@@ -42,7 +42,7 @@ _SIGNATURES = {
     "acx_pbfs_commit": (_I32, [_PTR, _PTR, _I32, _I64, _PTR, _PTR, _PTR, _I64, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR,
                                _PTR]),
     "acx_pbfs_expand2": (_I32, [_PTR, _PTR, _PTR, _PTR, _I64, _I64, _I32, _I32, _I32, _I64, _PTR, _PTR, _PTR, _PTR]),
-    "acx_pbfs_probe2": (_I32, [_PTR, _PTR, _I64, _I32, _I64, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR]),
+    "acx_pbfs_probe2": (_I32, [_PTR, _PTR, _I32, _PTR, _I64, _I32, _I64, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR]),
     "acx_pbfs_decide": (_I64, [_PTR, _PTR, _I64, _PTR, _I64, _I64, _PTR, _PTR, _I32, _I32, _PTR, _I64, _PTR]),
     "acx_pbfs_commit2": (_I32, [_PTR, _PTR, _I64, _I32, _I64, _PTR, _PTR, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR,
                                 _PTR]),

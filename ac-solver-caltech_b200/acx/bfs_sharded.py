@@ -72,6 +72,8 @@ class GpuShard:
     the data path (only the count all-gather, which doubles as the barrier).  transport "nccl": records are
     bucketed into a local send buffer and exchanged with an all-to-all-v."""
 
+    n_bufs = 2  # exchange buffers: round k + 1 may be staged while round k is still being probed / committed
+
     def __init__(self, m, cyclical, cap_local, max_parents, device, transport="auto"):
         self.m, self.rowb, self.cyc = m, 2 * m, bool(cyclical)
         self.rec = record_bytes(self.rowb)
@@ -113,7 +115,7 @@ class GpuShard:
             import ctypes
 
             self.recv_bufs, self.dst = [], []
-            for _ in range(2):
+            for _ in range(self.n_bufs):
                 ptr = ctypes.c_void_p()
                 _lib.check(self.L.acx_peer_alloc(nbytes, ctypes.byref(ptr)), "acx_peer_alloc")
                 self._own.append(ptr.value)
@@ -138,7 +140,7 @@ class GpuShard:
                 self.dst.append([bases[g] + rank * self.rcap * self.rec for g in range(G)])
         elif self.fused:
             # two send buffers: round k + 1 may be staged while round k is still being exchanged / probed
-            self.sends = [torch.empty((G * self.rcap, self.rec), dtype=torch.uint8, device=self.dev) for _ in range(2)]
+            self.sends = [torch.empty((G * self.rcap, self.rec), dtype=torch.uint8, device=self.dev) for _ in range(self.n_bufs)]
             self.dst = [[b.data_ptr() + g * self.rcap * self.rec for g in range(G)] for b in self.sends]
         self._group = group
         # frontier index buffers of a level (local index, global id), allocated once: a level can be most of the shard

@@ -27,7 +27,10 @@ STOP_SOLVED, STOP_ERROR, STOP_BUDGET = 1, 2, 3
 
 
 class PlaneShard2(PlaneShard):
-    """PlaneShard whose regions hold runs padded to whole 128-byte lines (four records)"""
+    """PlaneShard whose regions hold runs padded to whole 128-byte lines (four records).  Three exchange buffers: the
+    records of round k are read by probe k, commit k and -- as the previous round -- probe k+1, while round k+2 lands."""
+
+    n_bufs = 3
 
     def _region_cap(self, G, f):
         # every CTA of 256 parents pads each of its 3 x G runs by at most 3 null records
@@ -52,97 +55,166 @@ def make_plane_shard(root, cyclical, cap_local, max_parents, device, transport="
 
 
 class PlaneBFS(ShardedBFS):
-    def __init__(self, root, budget, shard, chunk=1 << 20, group=None):
+    """overlap=True (default): three streams form a pipeline over the rounds of a level --
+        stage   expand / exchange of round k+1 and its count all-gather
+        probe   probe of round k+1                      (follows probe k; needs the records of k+1 and the ring slot of k-1)
+        commit  mask all-reduce, scan, decision, commit of round k
+    The dependencies that remain: the all-gather of round k waits for this rank's probe of round k-1 and commit of round
+    k-2, so its completion means that every rank is there: the receive buffer that round k+1 lands in (one of three,
+    last read by probe k-1 as "previous round" and by commit k-2) is free everywhere; a provisional table entry met by probe k+1 belongs to round k+1 or to round k, whose records
+    are still in their receive buffer (acx_pbfs_probe2); decisions and commits stay in round order on one stream."""
+
+    def __init__(self, root, budget, shard, chunk=1 << 20, group=None, overlap=True):
         super().__init__(root, budget, shard, chunk=chunk, group=group)
         if self.world > 1 and shard.transport != "p2p":
             raise ValueError("PlaneBFS on more than one rank needs the peer-store transport")
         if self.chunk > (1 << 31) // 12 - 1:
             raise ValueError("chunk: the new nodes of a round are counted in 32 bits")
+        self.overlap = bool(overlap)
 
     def run(self):
         s, G, dev, L = self.shard, self.world, self.dev, self.shard.L
         rank, C_max = self.rank, self.chunk
-        stream = s.stream
         if s.owner_of_row(self.root, G) == rank:
             s.seed(self.root)
+        main = torch.cuda.current_stream(dev)
+        pipe = self.overlap and self.timers is None
+        st_stage = torch.cuda.Stream(dev, priority=-1) if pipe else main
+        st_commit = torch.cuda.Stream(dev) if pipe else main
         ctl = torch.zeros(16, dtype=torch.int64, device=dev)
         ctl[1] = 1
         c2 = (C_max + 1) // 2 * 2
-        mask16 = torch.zeros(c2, dtype=torch.int16, device=dev)
-        mask32 = mask16.view(torch.int32)
+        mask16 = [torch.zeros(c2, dtype=torch.int16, device=dev) for _ in range(2)]
+        mask32 = [m.view(torch.int32) for m in mask16]
+        mins = [torch.empty(2, dtype=torch.int64, device=dev) for _ in range(2)]
+        slot = [torch.empty(G * s.rcap, dtype=torch.int64, device=dev) for _ in range(2)]
         excl = torch.empty(C_max, dtype=torch.int32, device=dev)
-        mins = torch.empty(2, dtype=torch.int64, device=dev)
-        cursor = torch.zeros(G + 1, dtype=torch.int64, device=dev)
-        allc = torch.empty(G * (G + 1), dtype=torch.int64, device=dev)
-        slot = torch.empty(G * s.rcap, dtype=torch.int64, device=dev)
-        need = int(L.acx_pbfs_decide(0, 0, C_max, 0, 0, 0, 0, 0, 1, 0, 0, 0, stream))
+        cursors = [torch.zeros(G + 1, dtype=torch.int64, device=dev) for _ in range(3)]
+        allcs = [torch.empty(G * (G + 1), dtype=torch.int64, device=dev) for _ in range(3)]
+        need = int(L.acx_pbfs_decide(0, 0, C_max, 0, 0, 0, 0, 0, 1, 0, 0, 0, main.cuda_stream))
         if need < 0:
             _lib.check(need, "acx_pbfs_decide")
         temp = torch.empty(max(need, 1), dtype=torch.uint8, device=dev)
         recv = s.recv_bufs if s.transport == "p2p" else s.sends
-        dsts = [(ctypes.c_void_p * G)(*s.dst[b]) for b in range(2)]
+        dsts = [(ctypes.c_void_p * G)(*s.dst[b]) for b in range(3)]
         # the host runs at most `ahead` rounds in front of the device: it waits for the event of round k - ahead, looks
         # at that round's copy of the stop code (pinned memory) and stops enqueueing when the search has ended
         ahead = 4
         mirror = torch.zeros((ahead + 1, 16), dtype=torch.int64).pin_memory()
         events = [None] * (ahead + 1)
+        commit_ev, probed_ev = {}, {}  # round -> event behind its commit / its probe (the last few are kept)
         lo, hi, first = 0, 1, 0
+        n_local = s.n_local()
+
+        def stage(k, off, a, b):
+            """stage stream: expand the local parents of round k and route the records to their owners"""
+            cur = cursors[k % 3]
+            with torch.cuda.stream(st_stage):
+                cur.zero_()
+                if b > a:
+                    _lib.check(L.acx_pbfs_expand2(_ptr(s.nodes), _ptr(s.action), loc[a:b].data_ptr(), gids[a:b].data_ptr(), off, b - a,
+                                                  s.m, int(s.cyc), G, s.rcap, _ptr(cur), dsts[k % 3], _ptr(ctl), st_stage.cuda_stream), "acx_pbfs_expand2")
+            return cur
+
+        def gather(k, cur):
+            """stage stream: the count all-gather of round k, once this rank has committed round k-2 and probed round k-1 --
+            when it completes, every rank has written its records of round k and is done with the buffer (one of three)
+            that round k+1 will land in"""
+            allc = allcs[k % 3]
+            with torch.cuda.stream(st_stage):
+                if pipe:
+                    if (k - 2) in commit_ev:
+                        st_stage.wait_event(commit_ev[k - 2])
+                    if (k - 1) in probed_ev:
+                        st_stage.wait_event(probed_ev[k - 1])
+                if G > 1:
+                    dist.all_gather_into_tensor(allc, cur, group=self.group)
+                ev = torch.cuda.Event()
+                ev.record(st_stage)
+            return (allc if G > 1 else cur), ev
+
         while lo < hi:
             self.levels.append(hi - lo)
             self._tick(None)
-            n_local = s.n_local()
             gl = s.gid[first:n_local]
             nwin = (hi - lo + C_max - 1) // C_max
-            loc, gids, cuts = s.window_partition(gl, first, lo, C_max, nwin)
+            if nwin == 1:  # one round: the local frontier as it is (no grouping pass, no read-back)
+                loc, gids, cuts = torch.arange(first, n_local, dtype=torch.int64, device=dev), gl, [0, n_local - first]
+            else:
+                loc, gids, cuts = s.window_partition(gl, first, lo, C_max, nwin)
             first = n_local
             self._tick("level_sort")
-            for i, off in enumerate(range(lo, hi, C_max)):
+            offs = list(range(lo, hi, C_max))
+            if pipe:
+                st_stage.wait_stream(main)  # loc / gids of this level; every commit of the previous level (joined below)
+                st_commit.wait_stream(main)
+            cur = stage(self.rounds, offs[0], cuts[0], cuts[1])
+            self._tick("expand_exchange")
+            pending = gather(self.rounds, cur)
+            self._tick("count_allgather")
+            for i, off in enumerate(offs):
                 C = min(C_max, hi - off)
-                a, b = cuts[i], cuts[i + 1]
                 k = self.rounds
                 ring = k % (ahead + 1)
                 if events[ring] is not None:
                     events[ring].synchronize()
                     if int(mirror[ring, 0]) != 0:
                         break
-                buf = recv[k % 2]
-                cursor.zero_()
-                if b > a:
-                    _lib.check(L.acx_pbfs_expand2(_ptr(s.nodes), _ptr(s.action), loc[a:b].data_ptr(), gids[a:b].data_ptr(), off, b - a,
-                                                  s.m, int(s.cyc), G, s.rcap, _ptr(cursor), dsts[k % 2], _ptr(ctl), stream), "acx_pbfs_expand2")
+                r2 = k % 2
+                buf, prev = recv[k % 3], recv[(k + 2) % 3]
+                counts, ready = pending
+                nxt = stage(k + 1, offs[i + 1], cuts[i + 1], cuts[i + 2]) if i + 1 < len(offs) else None
                 self._tick("expand_exchange")
-                if G > 1:
-                    dist.all_gather_into_tensor(allc, cursor, group=self.group)
-                    counts = allc
-                else:
-                    counts = cursor
                 rc_ptr = counts.data_ptr() + 8 * rank  # records rank s staged for this rank: counts[s * (G + 1) + rank]
-                self._tick("count_allgather")
-                mask16[: (C + 1) // 2 * 2].zero_()
-                mins.fill_(SENT)
-                _lib.check(L.acx_pbfs_probe2(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(s.table), s.tcap, _ptr(s.nodes), _ptr(slot), _ptr(mins),
-                                             _ptr(mask32), _ptr(ctl), stream), "acx_pbfs_probe2")
+                # ---- probe stream (main)
+                if pipe:
+                    main.wait_event(ready)
+                    if (k - 2) in commit_ev:
+                        main.wait_event(commit_ev[k - 2])  # slot / mask / mins of this ring position are free again
+                mask16[r2][: (C + 1) // 2 * 2].zero_()
+                mins[r2].fill_(SENT)
+                _lib.check(L.acx_pbfs_probe2(_ptr(buf), _ptr(prev), k & 1, rc_ptr, G + 1, G, s.rcap, _ptr(s.table), s.tcap, _ptr(s.nodes),
+                                             _ptr(slot[r2]), _ptr(mins[r2]), _ptr(mask32[r2]), _ptr(ctl), main.cuda_stream), "acx_pbfs_probe2")
                 self._tick("probe")
-                if G > 1:
-                    if self.timers is not None:
-                        dist.barrier(group=self.group)
-                        self._tick("wait_slowest_rank")
-                    dist.all_reduce(mask32[: (C + 1) // 2], group=self.group)
-                    dist.all_reduce(mins, op=dist.ReduceOp.MIN, group=self.group)
-                rcd = int(L.acx_pbfs_decide(_ptr(mask16), _ptr(excl), C, _ptr(mins), off, self.budget, _ptr(ctl), _ptr(counts), G, rank,
-                                            _ptr(temp), need, stream))
-                if rcd:
-                    _lib.check(rcd, "acx_pbfs_decide")
-                self._tick("reduce_scan_decide")
-                _lib.check(L.acx_pbfs_commit2(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(slot), _ptr(excl), _ptr(mask32), off, _ptr(ctl),
-                                              _ptr(s.n_local_dev), _ptr(s.table), _ptr(s.nodes), _ptr(s.gid), _ptr(s.parent), _ptr(s.action),
-                                              stream), "acx_pbfs_commit2")
-                self._tick("commit")
-                mirror[ring].copy_(ctl, non_blocking=True)
-                events[ring] = torch.cuda.Event()
-                events[ring].record()
+                probed = torch.cuda.Event()
+                probed.record(main)
+                probed_ev[k] = probed
+                probed_ev.pop(k - 3, None)
+                # ---- commit stream
+                with torch.cuda.stream(st_commit):
+                    if pipe:
+                        st_commit.wait_event(probed)
+                    if G > 1:
+                        if self.timers is not None:
+                            dist.barrier(group=self.group)
+                            self._tick("wait_slowest_rank")
+                        dist.all_reduce(mask32[r2][: (C + 1) // 2], group=self.group)
+                        dist.all_reduce(mins[r2], op=dist.ReduceOp.MIN, group=self.group)
+                    cs = st_commit.cuda_stream
+                    rcd = int(L.acx_pbfs_decide(_ptr(mask16[r2]), _ptr(excl), C, _ptr(mins[r2]), off, self.budget, _ptr(ctl), _ptr(counts), G,
+                                                rank, _ptr(temp), need, cs))
+                    if rcd:
+                        _lib.check(rcd, "acx_pbfs_decide")
+                    self._tick("reduce_scan_decide")
+                    _lib.check(L.acx_pbfs_commit2(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(slot[r2]), _ptr(excl), _ptr(mask32[r2]), off,
+                                                  _ptr(ctl), _ptr(s.n_local_dev), _ptr(s.table), _ptr(s.nodes), _ptr(s.gid), _ptr(s.parent),
+                                                  _ptr(s.action), cs), "acx_pbfs_commit2")
+                    self._tick("commit")
+                    commit_ev[k] = torch.cuda.Event()
+                    commit_ev[k].record(st_commit)
+                    commit_ev.pop(k - 3, None)
+                    mirror[ring].copy_(ctl, non_blocking=True)
+                    events[ring] = torch.cuda.Event()
+                    events[ring].record(st_commit)
                 self.rounds += 1
-            c = ctl.tolist()  # the one read-back of the level
+                if nxt is not None:
+                    pending = gather(k + 1, nxt)
+                    self._tick("count_allgather")
+            if pipe:  # join: the level's commits, and a staged round that may still be in flight after an early exit
+                main.wait_stream(st_commit)
+                main.wait_stream(st_stage)
+            c = torch.cat([ctl, s.n_local_dev]).tolist()  # the one read-back of the level
+            n_local = c[16]
             self.n_nodes, self.n_expanded = c[1], c[2]
             if c[6]:
                 raise RuntimeError("plane bfs: a send region overflowed (hash imbalance above the 15% head room)")

@@ -36,6 +36,7 @@ enum { CTL_STOP = 0, CTL_NODES = 1, CTL_EXPANDED = 2, CTL_GID_BASE = 3, CTL_POS 
        CTL_STAGED = 8, CTL_STAGED_LOCAL = 9 };
 enum { STOP_NONE = 0, STOP_SOLVED = 1, STOP_ERROR = 2, STOP_BUDGET = 3 };
 static constexpr unsigned long long PB_SENT = 1ull << 62;
+static constexpr uint64_t PB_IDX = (1ull << 46) - 1;  // candidate index inside a provisional entry
 
 struct PbDst2 {
     uint8_t* region[PB_MAX_WORLD];
@@ -187,6 +188,8 @@ __global__ void __launch_bounds__(EX_THREADS) k_pbfs_expand2(const uint64_t* __r
 }
 
 struct Pb2Params {
+    const uint64_t* recs_prev;    // the records of the previous round (its claims may still be provisional in the table)
+    uint64_t parity;              // of this round: provisional entries carry it in bit 46 of the value
     const uint64_t* recs;         // nreg regions of rcap records
     const int64_t* region_counts; // device: records (incl. null padding) in region s = region_counts[s * count_stride]
     int64_t count_stride;
@@ -244,7 +247,7 @@ __global__ void __launch_bounds__(256) k_pbfs_probe2(const Pb2Params p) {
     const PWords st = pb_state(rec);
     const uint64_t h = pb_hash(st);
     const uint64_t tag = ((h >> 48) | 1ull) << 48;
-    const uint64_t mine = tag | PB_PROV | (uint64_t)j;
+    const uint64_t mine = tag | PB_PROV | (p.parity << 46) | (uint64_t)j;
     const uint64_t mask = (uint64_t)p.tcap - 1;
     uint64_t slot = (h ^ (h >> 23)) & mask;
     for (;;) {
@@ -260,9 +263,17 @@ __global__ void __launch_bounds__(256) k_pbfs_probe2(const Pb2Params p) {
             e = old;
         }
         if ((e >> 48) == (tag >> 48)) {
-            if (e & PB_PROV) {
+            if ((e & PB_PROV) && ((e >> 46) & 1ull) != p.parity) {
+                // a claim of the PREVIOUS round that its commit (running next to this probe) has not turned into a node
+                // yet: every candidate of that round precedes this one in the reference's order, so an equal state is visited
+                const PWords orec = pb_load(p.recs_prev + 4 * (int64_t)(e & PB_IDX));
+                if (pb_equal(st, pb_state(orec))) {
+                    p.slot[j] = -1;
+                    return;
+                }
+            } else if (e & PB_PROV) {
                 for (;;) {
-                    const int64_t other = (int64_t)(e & PB_VAL);
+                    const int64_t other = (int64_t)(e & PB_IDX);
                     const PWords orec = pb_load(p.recs + 4 * other);
                     if (!pb_equal(st, pb_state(orec))) break;
                     const int64_t oord = pb_order(orec);
@@ -285,7 +296,7 @@ __global__ void __launch_bounds__(256) k_pbfs_probe2(const Pb2Params p) {
                 }
             } else {
                 const int64_t id = (int64_t)(e & PB_VAL);
-                if (pb_equal(st, pb_load(p.nodes + 4 * id))) {
+                if (pb_equal(st, pb_load_cg(p.nodes + 4 * id))) {  // the previous round's commit may be appending nodes right now
                     p.slot[j] = -1;
                     return;
                 }
@@ -386,8 +397,10 @@ __global__ void __launch_bounds__(256) k_pbfs_commit2(const Pb2Params p) {
     p.gid[id] = gid;
     p.parent[id] = p.parent_base + par;
     p.action[id] = (uint8_t)act;
+    // the probe of the next round may run next to this kernel: the node must be visible before the slot names it
+    __threadfence();
     // the slot keeps its tag (recomputed from the state: no read of the random table line) and now names the node
-    p.table[sl] = (((pb_hash(st) >> 48) | 1ull) << 48) | (uint64_t)id;
+    __stcg(p.table + sl, (((pb_hash(st) >> 48) | 1ull) << 48) | (uint64_t)id);
 }
 
 }  // namespace acx
@@ -441,13 +454,16 @@ static int pb2_common(Pb2Params& p, const uint64_t* recs, const int64_t* region_
     return ACX_OK;
 }
 
-extern "C" int acx_pbfs_probe2(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap,
-                               uint64_t* table, int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins,
+extern "C" int acx_pbfs_probe2(const uint64_t* recs, const uint64_t* recs_prev, int parity, const int64_t* region_counts_dev,
+                               int64_t count_stride, int n_regions, int64_t region_cap, uint64_t* table, int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins,
                                uint32_t* mask32, const int64_t* ctl, acx_stream_t stream) {
     if (tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe2: table capacity must be a power of two");
     Pb2Params p = {};
     if (int rc = pb2_common(p, recs, region_counts_dev, count_stride, n_regions, region_cap, "acx_pbfs_probe2")) return rc;
-    if (!table || !nodes || !slot || !mins || !mask32 || !ctl) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe2: null pointer");
+    if (!table || !nodes || !slot || !mins || !mask32 || !ctl || !recs_prev) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe2: null pointer");
+    if ((int64_t)n_regions * region_cap > (int64_t)PB_IDX) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe2: too many records per round");
+    p.recs_prev = recs_prev;
+    p.parity = (uint64_t)(parity & 1);
     p.table = table; p.tcap = tcap; p.nodes = nodes; p.slot = slot;
     p.mins = reinterpret_cast<unsigned long long*>(mins); p.mask32 = mask32; p.ctl = const_cast<int64_t*>(ctl);
     const dim3 grid((unsigned)((region_cap + 255) / 256), (unsigned)n_regions);

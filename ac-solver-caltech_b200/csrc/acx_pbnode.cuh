@@ -29,6 +29,13 @@ __device__ __forceinline__ PWords pb_load(const uint64_t* p) {
     return o;
 }
 
+// the same load served by L2: for data another kernel may be writing while this one runs (an L1 line could be stale)
+__device__ __forceinline__ PWords pb_load_cg(const uint64_t* p) {
+    PWords o;
+    asm volatile("ld.global.cg.v4.b64 {%0, %1, %2, %3}, [%4];" : "=l"(o.w[0]), "=l"(o.w[1]), "=l"(o.w[2]), "=l"(o.w[3]) : "l"(p) : "memory");
+    return o;
+}
+
 __device__ __forceinline__ void pb_store(uint64_t* p, const PWords& v) {
     asm volatile("st.global.v4.b64 [%0], {%1, %2, %3, %4};" ::"l"(p), "l"(v.w[0]), "l"(v.w[1]), "l"(v.w[2]), "l"(v.w[3]) : "memory");
 }

@@ -36,7 +36,7 @@ def _make_engine(root, budget, cyclical, world, dev, chunk, prof=False):
 
         shard = make_plane_shard(root, cyclical, cap_local, max_parents, str(dev), transport=transport)
         if shard is not None:
-            eng = PlaneBFS(root, budget, shard, chunk=chunk)
+            eng = PlaneBFS(root, budget, shard, chunk=chunk, overlap=os.environ.get("ACX_BFS_OVERLAP", "1") != "0")
             if prof:
                 eng.timers = {}
             return eng, shard

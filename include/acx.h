@@ -265,14 +265,18 @@ int acx_pbfs_commit(const uint64_t* recs, const int64_t* region_counts, int n_re
  *   acx_pbfs_probe2   region counts are a DEVICE array; the winner resolution is fused in: mask32 (uint32 view of one
  *                     uint16 per parent, caller zeroes) has bit a of parent p set iff child (p, a) is the first discovery
  *                     of a new state, slot[j] >= 0 exactly for those candidates; mins = {min success order, min error
- *                     order} (caller sets both to 2^62).
+ *                     order} (caller sets both to 2^62).  `parity` (round number & 1) tags the provisional entries of
+ *                     this round; an entry of the other parity belongs to the previous round, whose records are still
+ *                     at recs_prev and whose commit may run NEXT TO this probe: an equal state there is visited
+ *                     (every candidate of an earlier round precedes this one in the reference's order).
  *   acx_pbfs_decide   exclusive scan of popcount(mask16) -> excl_out (int32), then the decision of the round
  *                     (breadth_first.py:84-95 in the reference's order) into ctl.  temp == NULL returns the scratch size.
  *   acx_pbfs_commit2  claim holders become nodes with global id ctl[3] + excl[p] + popcount(mask16[p] & bits below a). */
 int acx_pbfs_expand2(const uint64_t* nodes, const uint8_t* action, const int64_t* loc, const int64_t* gids, int64_t ord_base,
                      int64_t f, int m, int cyclical, int world, int64_t region_cap, uint64_t* cursor,
                      uint8_t* const* dst_regions, const int64_t* ctl, acx_stream_t stream);
-int acx_pbfs_probe2(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap, uint64_t* table,
+int acx_pbfs_probe2(const uint64_t* recs, const uint64_t* recs_prev, int parity, const int64_t* region_counts_dev, int64_t count_stride,
+                    int n_regions, int64_t region_cap, uint64_t* table,
                     int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins, uint32_t* mask32, const int64_t* ctl,
                     acx_stream_t stream);
 int64_t acx_pbfs_decide(const uint16_t* mask16, int32_t* excl_out, int64_t n_parents, const uint64_t* mins, int64_t parent_base,
