@@ -14,16 +14,48 @@ from acx import batch
 
 
 class _Discrete:
+    """stand-in for gymnasium.spaces.Discrete when gymnasium is not installed"""
+
     def __init__(self, n):
-        self.n = n
+        self.n, self.shape, self.dtype = n, (), np.int64
 
     def sample(self):
         return int(np.random.randint(self.n))
 
+    def contains(self, x):
+        return isinstance(x, (int, np.integer)) and 0 <= int(x) < self.n
+
 
 class _Box:
+    """stand-in for gymnasium.spaces.Box when gymnasium is not installed"""
+
     def __init__(self, low, high, dtype):
         self.low, self.high, self.dtype, self.shape = low, high, dtype, low.shape
+
+    def sample(self):
+        return np.random.randint(self.low, self.high + 1).astype(self.dtype)
+
+    def contains(self, x):
+        x = np.asarray(x)
+        return x.shape == self.shape and bool(np.all(x >= self.low)) and bool(np.all(x <= self.high))
+
+
+# The reference's ACEnv is a gymnasium.Env (ac_env.py:8-9,53) with gymnasium spaces, which gymnasium's wrappers
+# (NormalizeReward, TransformReward) and SyncVectorEnv check for.  With gymnasium installed the drop-in is one too;
+# without it (this image) the stand-ins above provide shape / n / dtype / sample / contains.
+try:  # pragma: no cover - depends on the environment
+    import gymnasium as _gym
+    from gymnasium.spaces import Box as _GymBox, Discrete as _GymDiscrete
+
+    _EnvBase = _gym.Env
+
+    def _make_spaces(m):
+        return (_GymBox(np.ones(m * 2, dtype=np.int8) * -2, np.ones(m * 2, dtype=np.int8) * 2, dtype=np.int8), _GymDiscrete(12))
+except ImportError:
+    _EnvBase = object
+
+    def _make_spaces(m):
+        return _Box(np.ones(m * 2, dtype=np.int8) * -2, np.ones(m * 2, dtype=np.int8) * 2, np.int8), _Discrete(12)
 
 
 @dataclass
@@ -55,7 +87,7 @@ class ACEnvConfig:
                    use_supermoves=config_dict.get("use_supermoves", cls().use_supermoves))
 
 
-class ACEnv:
+class ACEnv(_EnvBase):
     def __init__(self, config: ACEnvConfig = None):
         config = config if config is not None else ACEnvConfig()
         self.n_gen = 2
@@ -65,8 +97,7 @@ class ACEnv:
         if config.use_supermoves:
             raise NotImplementedError("ACEnv with supermoves is not yet implemented in this library.")
         m = self.max_relator_length
-        self.observation_space = _Box(np.ones(m * 2, dtype=np.int8) * -2, np.ones(m * 2, dtype=np.int8) * 2, np.int8)
-        self.action_space = _Discrete(12)
+        self.observation_space, self.action_space = _make_spaces(m)
         self.max_reward = self.horizon_length * m * self.n_gen
         self._dev = _device.device()
         self._load(self.initial_state)

@@ -20,6 +20,7 @@
 // reading anything back and looks at the control block once per level.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/acx.h"
@@ -223,7 +224,8 @@ __device__ __forceinline__ void mask_clear(unsigned* mask32, int64_t ord) {
 // Table slot = tag(16) | PROV(1) | value(47): value = node id, or (PROV) the index of the candidate that currently
 // claims the state in this round.  slot[j] >= 0 and the mask bit of j are set exactly for the claim holders when the
 // kernel ends: the first discovery (smallest order) of every new state.
-__global__ void __launch_bounds__(256) k_pbfs_probe2(const Pb2Params p) {
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) k_pbfs_probe2(const Pb2Params p) {
     if (p.ctl[CTL_STOP] != 0) return;
     const int64_t s = blockIdx.y, i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // region, record in the region
     if (i >= p.region_counts[s * p.count_stride]) return;
@@ -467,7 +469,13 @@ extern "C" int acx_pbfs_probe2(const uint64_t* recs, const uint64_t* recs_prev, 
     p.table = table; p.tcap = tcap; p.nodes = nodes; p.slot = slot;
     p.mins = reinterpret_cast<unsigned long long*>(mins); p.mask32 = mask32; p.ctl = const_cast<int64_t*>(ctl);
     const dim3 grid((unsigned)((region_cap + 255) / 256), (unsigned)n_regions);
-    k_pbfs_probe2<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    static const int occ = [] {  // ACX_PROBE_OCC=5|6|8 resident CTAs per SM (registers 44 / 40 / 32): tuning knob
+        const char* e = getenv("ACX_PROBE_OCC");
+        return e ? atoi(e) : 6;
+    }();
+    if (occ >= 8) k_pbfs_probe2<8><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else if (occ == 6) k_pbfs_probe2<6><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else k_pbfs_probe2<5><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }

@@ -102,11 +102,24 @@ struct Inst {
     uint64_t tmask;
 };
 
+// Python's tuple order (total, depth, state as signed ints) of greedy.py:104-113, in stages: the (total | depth) field,
+// the true depth when the 16-bit field saturated, then the 13 leading letters -- decided by the 3-bit codes only when no
+// letter in front of the first differing code was clamped (|letter| >= 3 all map to code 0 / 6) -- else the full rows.
 __device__ __forceinline__ bool node_less(const Inst& I, int32_t a, int32_t b) {
     const uint64_t ka = I.key[a], kb = I.key[b];
-    if (ka != kb) return ka < kb;
-    const int da = I.depth[a], db = I.depth[b];  // only differs from the key when saturated
-    if (da != db) return da < db;
+    const uint64_t ha = ka >> 39, hb = kb >> 39;
+    if (ha != hb) return ha < hb;
+    if ((ha & 0xFFFFull) == 0xFFFFull) {
+        const int da = I.depth[a], db = I.depth[b];
+        if (da != db) return da < db;
+    }
+    const uint64_t low = (1ull << 39) - 1, la = ka & low, lb = kb & low;
+    if (la != lb) {
+        const int g = (63 - __clzll((long long)(la ^ lb))) / 3;                    // group of the first differing code
+        const uint64_t above = low & ~((1ull << (3 * (g + 1))) - 1);               // the codes in front of it (equal in both)
+        const uint64_t clamped = ~la & ~((la >> 1) ^ (la >> 2)) & 0x1249249249ull;  // codes 0 and 6
+        if ((clamped & above) == 0ull) return la < lb;
+    }
     return row_less(reinterpret_cast<const uint32_t*>(I.nodes + (size_t)a * I.pitch),
                     reinterpret_cast<const uint32_t*>(I.nodes + (size_t)b * I.pitch), I.nwords);
 }

@@ -1,4 +1,5 @@
-"""GPU parity of acx.beam against a literal restatement of the reference's beam_search
+"""GPU parity of acx.beam: against the reference itself (beam_golden.json, bottom of this file) and -- as a
+debugging aid with arbitrary float models -- against a literal restatement of the reference's beam_search
 (value_search/value_guided_search.py:417-561) that uses the oracle's ACMove, numpy compute_features
 (value_search/feature_extraction.py:11-91) and the same torch model on the same device for scoring."""
 import numpy as np
@@ -246,3 +247,97 @@ def test_value_guided_greedy_vs_reference_restatement(cuda, oracle, golden_dir, 
         assert got == want, (len(row), budget, cyc)
         n_solved += int(want[0])
     assert n_solved >= 1 or mode != "length"
+
+
+# ---- parity with the reference ITSELF: tests/golden/beam_golden.json (made by tests/golden/make_beam_golden.py) -------
+def _golden_models(g, dev):
+    """the value networks of the fixture, re-built from their state_dicts (the layer stacks of value_search/value_network.py
+    FeatureMLP / SequenceValueNet with dropout 0: Linear-ReLU-...-Linear, Embedding-Conv1d-ReLU-mean-Linear-ReLU-Linear)"""
+    import torch
+
+    def tensor(e):
+        return torch.tensor(e["data"], dtype=torch.float32).reshape(e["shape"])
+
+    def mlp(sd, hidden):
+        layers, prev = [], 14
+        for h in hidden:
+            layers += [torch.nn.Linear(prev, h), torch.nn.ReLU(), torch.nn.Dropout(0.0)]
+            prev = h
+        layers.append(torch.nn.Linear(prev, 1))
+        net = torch.nn.Sequential(*layers)
+        net.load_state_dict({k[len("net."):]: tensor(v) for k, v in sd.items()})
+        return net.to(dev).eval()
+
+    class Seq(torch.nn.Module):
+        def __init__(self, embed_dim, num_conv_layers, conv_channels, kernel_size, mlp_hidden, max_seq_len):
+            super().__init__()
+            self.embedding = torch.nn.Embedding(5, embed_dim, padding_idx=2)
+            conv, cin = [], embed_dim
+            for _ in range(num_conv_layers):
+                conv += [torch.nn.Conv1d(cin, conv_channels, kernel_size, padding=kernel_size // 2), torch.nn.ReLU(), torch.nn.Dropout(0.0)]
+                cin = conv_channels
+            self.conv = torch.nn.Sequential(*conv)
+            self.head = torch.nn.Sequential(torch.nn.Linear(conv_channels, mlp_hidden), torch.nn.ReLU(), torch.nn.Dropout(0.0),
+                                            torch.nn.Linear(mlp_hidden, 1))
+
+        def forward(self, t):
+            x = self.conv(self.embedding(t).transpose(1, 2))
+            return self.head(x.mean(dim=2))
+
+    seq = Seq(**g["seq_kwargs"])
+    seq.load_state_dict({k: tensor(v) for k, v in g["seq_state_dict"].items()})
+    return {"mlp": mlp(g["mlp_state_dict"], g["mlp_hidden_dims"]), "len": mlp(g["len_state_dict"], g["len_hidden_dims"]),
+            "seq": seq.to(dev).eval()}
+
+
+def _golden_stats(name, g):
+    if name == "len":
+        return np.zeros(14, dtype=np.float32), np.ones(14, dtype=np.float32)
+    return np.array(g["feat_mean"], dtype=np.float32), np.array(g["feat_std"], dtype=np.float32)
+
+
+def test_beam_search_matches_the_reference(cuda, golden_dir):
+    """value_search.beam_search of the reference, run with fixed-weight value networks (exact float32 scores), against
+    acx.beam.beam_search with the same weights on the GPU: (solved, path, stats) for k in {1, 10, 50}, budgets {100, 3000}"""
+    import json
+    import os
+
+    from acx.beam import beam_search
+
+    with open(os.path.join(golden_dir, "beam_golden.json")) as f:
+        g = json.load(f)
+    models = _golden_models(g, cuda)
+    n_solved = 0
+    for c in g["beam"]:
+        mean, std = _golden_stats(c["model"], g)
+        got = beam_search(np.array(c["presentation"], dtype=np.int8), models[c["model"]], architecture=c["arch"], feat_mean=mean,
+                          feat_std=std, beam_width=c["beam_width"], max_nodes_to_explore=c["budget"], device=str(cuda),
+                          cyclically_reduce_after_moves=c["cyclical"])
+        want = (c["solved"], [tuple(p) for p in c["path"]], c["stats"])
+        assert (got[0], [tuple(p) for p in got[1]], {k: v for k, v in got[2].items() if k != "time"}) == want, \
+            (c["model"], c["beam_width"], c["budget"], c["cyclical"], c["presentation"])
+        n_solved += int(c["solved"])
+    assert n_solved >= 10 and len(g["beam"]) >= 200
+
+
+def test_value_guided_greedy_matches_the_reference(cuda, golden_dir):
+    """value_guided_greedy_search of the reference with a model (value_guided_search.py:253-414) against acx.beam"""
+    import json
+    import os
+
+    from acx.beam import value_guided_greedy_search
+
+    with open(os.path.join(golden_dir, "beam_golden.json")) as f:
+        g = json.load(f)
+    models = _golden_models(g, cuda)
+    n_solved = 0
+    for c in g["vgreedy"]:
+        mean, std = _golden_stats(c["model"], g)
+        got = value_guided_greedy_search(np.array(c["presentation"], dtype=np.int8), models[c["model"]], architecture=c["arch"],
+                                         feat_mean=mean, feat_std=std, max_nodes_to_explore=c["budget"], device=str(cuda),
+                                         cyclically_reduce_after_moves=c["cyclical"])
+        want = (c["solved"], [tuple(p) for p in c["path"]], c["stats"])
+        assert (got[0], [tuple(p) for p in got[1]], {k: v for k, v in got[2].items() if k != "time"}) == want, \
+            (c["model"], c["budget"], c["cyclical"], c["presentation"])
+        n_solved += int(c["solved"])
+    assert n_solved >= 3
