@@ -255,6 +255,10 @@ def other_configs(dev):
 
 
 def gpu_arm(args):
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        # NCCL's INFO lines go to stdout on this image (NCCL_DEBUG_FILE is not honoured by the bundled library) and stdout
+        # must stay the one JSON line: keep NCCL quiet and report the communicator's size on stderr instead (below)
+        os.environ.setdefault("NCCL_DEBUG", "WARN")
     import torch
     import torch.distributed as dist
 
@@ -268,10 +272,6 @@ def gpu_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # the communicator's own "rank r nranks N" lines go to stderr; stdout stays the one JSON line
-        os.environ.setdefault("NCCL_DEBUG", "INFO")
-        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
         probe = torch.ones(1, device=dev)
         dist.all_reduce(probe)

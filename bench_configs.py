@@ -136,7 +136,8 @@ def cfg_ppo(dev, n=65536, T=64):
                     logits = actor(x)
                     val_buf[t].copy_(critic(x).squeeze(-1))
                     logp = torch.log_softmax(logits, dim=-1)
-                    a = torch.multinomial(logp.exp(), 1).squeeze(-1)
+                    # Categorical(logits).sample() as a Gumbel arg-max (one fused elementwise pass instead of multinomial)
+                    a = (logp - torch.log(-torch.log(torch.rand_like(logp).clamp_min(1e-20)))).argmax(dim=-1)
                     logp_buf[t].copy_(logp.gather(1, a[:, None]).squeeze(-1))
                     act_buf[t].copy_(a)
             batch.env_step(buf, act_buf[t], next_idx=env.next_state_index, clip=env.clip, chained=not with_policy,
