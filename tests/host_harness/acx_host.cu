@@ -89,9 +89,71 @@ static void run_cert36_split(const int8_t* in, const uint8_t* moves, int8_t* out
     }
 }
 
+// register-resident conjugations of the frontier expansion (conj_row_words of csrc/acx_envrow.cuh, used by
+// csrc/acx_expand.cu): the plain form when the search does not reduce cyclically, the rotation form on certified rows
+// when it does; everything else through the checked row function
+template <bool CERT>
+static int conj_words36(uint8_t* ia, uint32_t d, int n) {
+    const int m = 36;
+    const bool i = d & 1u;
+    const uint32_t mag = 1u + ((d >> 3) & 1u), neg = 0x100u - mag;
+    const uint32_t g = (d & 4u) ? neg : mag, gi = (d & 4u) ? mag : neg;
+    const uint8_t* rel = ia + (i ? m : 0);
+    const bool sc = rel[0] == gi, ec = rel[n - 1] == g;
+    uint32_t w[18], o[18], fv = 0;
+    int fp = -1;
+    memcpy(w, ia, 72);
+    const int nn = conj_row_words<36, CERT>(w, o, i, n, sc, ec, d, fp, fv);
+    memcpy(ia, o, 72);
+    if (fp >= 0) ia[fp] = (uint8_t)fv;
+    return nn;
+}
+
+static void run_conj_words36(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status, int64_t n,
+                             int cyc) {
+    const int m = 36, rowb = 72;
+    std::vector<uint64_t> a(rowb / 8 + 4);
+    for (int64_t r = 0; r < n; ++r) {
+        uint8_t* ia = reinterpret_cast<uint8_t*>(a.data()) + 8;
+        memcpy(ia, in + r * rowb, rowb);
+        int l0 = -1, l1 = -1;
+        uint32_t st = 99;
+        const uint32_t d = decode_move(moves[r]);
+        bool done = false;
+        if (d & 2u) {
+            if (cyc) {
+                if (row_is_certified(ia, m, l0, l1)) {
+                    conj_words36<true>(ia, d, (d & 1u) ? l1 : l0);
+                    st = ACX_ROW_OK;
+                    done = true;
+                }
+            } else {
+                Raw64 raw[2];
+                uint32_t chk;
+                pack_row_static64<36>(ia, raw, chk);
+                R64 rr[2];
+                int cnt[2];
+                if (classify_row64(raw, chk, rr, cnt) == ROW_FAST) {
+                    const int nn = conj_words36<false>(ia, d, cnt[d & 1u]);
+                    l0 = (d & 1u) ? cnt[0] : nn;
+                    l1 = (d & 1u) ? nn : cnt[1];
+                    st = ACX_ROW_OK;
+                    done = true;
+                }
+            }
+        }
+        if (!done) acmove_row64<36>(ia, m, moves[r], cyc != 0, l0, l1, st);
+        memcpy(out + r * rowb, ia, rowb);
+        lens[2 * r] = (uint8_t)l0;
+        lens[2 * r + 1] = (uint8_t)l1;
+        status[r] = (uint8_t)st;
+    }
+}
+
 // variant: 0 = dynamic width (generic planes), 1 = static generic planes (m must be 36 or 128),
 //          2 = 64-bit planes dynamic (m <= 64), 3 = 64-bit planes static (m == 36),
-//          4 = certified-row env path (m == 36, cyclical only), 5/6 = class-split certified step (acx_envrow.cuh)
+//          4 = certified-row env path (m == 36, cyclical only), 5/6 = class-split certified step (acx_envrow.cuh),
+//          7 = register-resident conjugations of the frontier expansion (m == 36)
 extern "C" int acxh_move_batch(const int8_t* in, const uint8_t* moves, int8_t* out, uint8_t* lens, uint8_t* status,
                                int64_t n, int m, int cyc, int variant, int inplace) {
     if (variant == 4) {
@@ -102,6 +164,11 @@ extern "C" int acxh_move_batch(const int8_t* in, const uint8_t* moves, int8_t* o
     if (variant == 5 || variant == 6) {  // class-split certified step; 6 = padding filled with 0xFF instead of 0
         if (m != 36 || !cyc) return -1;
         run_cert36_split(in, moves, out, lens, status, n, variant == 6 ? 0xFF : 0x00);
+        return 0;
+    }
+    if (variant == 7) {
+        if (m != 36) return -1;
+        run_conj_words36(in, moves, out, lens, status, n, cyc);
         return 0;
     }
     if (variant == 2) {

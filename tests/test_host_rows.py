@@ -72,3 +72,29 @@ def test_host_certified_rows(oracle, golden_dir):
             assert np.array_equal(o, eo)
             assert np.array_equal(l.astype(np.int32), el)
             assert np.array_equal(st, es)
+
+
+@pytest.mark.parametrize("cyc", [0, 1])
+def test_host_register_conjugations(oracle, golden_dir, cyc):
+    """the register-resident conjugations of the frontier expansion (conj_row_words of acx_envrow.cuh, both forms):
+    relators of every length up to the guard (n + 2 > m leaves the word alone), both cancellations"""
+    from helpers import dataset_rows, walk_states
+
+    roots = dataset_rows(golden_dir)
+    states = walk_states(oracle, roots, 36, 4000, 40, seed=11, cyclical=bool(cyc))
+    rng = np.random.default_rng(13)
+    full = random_rows(rng, 4000, 36, kinds=(1,))  # freely reduced, every length 1..36
+    short = random_rows(rng, 2000, 36, kinds=(1,))
+    short[:, 3:36] = 0
+    short[:, 36 + 2:] = 0
+    mixed = random_rows(rng, 2000, 36)
+    rows = np.concatenate([states, full, short, mixed])
+    for rep in range(3):
+        mv = rng.integers(4, 12, len(rows)).astype(np.uint8)
+        if rep == 2:
+            mv = rng.integers(0, 12, len(rows)).astype(np.uint8)
+        eo, el, es = oracle.acmove_batch(rows, mv, cyclical=cyc, threads=4)
+        o, l, st = harness.move_batch(rows, mv, cyc, 7, 1)
+        assert np.array_equal(o, eo)
+        assert np.array_equal(l.astype(np.int32), el)
+        assert np.array_equal(st, es)
