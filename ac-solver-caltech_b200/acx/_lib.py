@@ -47,6 +47,7 @@ _SIGNATURES = {
     "acx_pbfs_commit2": (_I32, [_PTR, _PTR, _I64, _I32, _I64, _PTR, _PTR, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR,
                                 _PTR]),
     "acx_bfs_mask_scan": (_I64, [_PTR, _I64, _PTR, _PTR, _PTR, _I64, _PTR]),
+    "acx_bfs_mask_scan_static": (_I32, [_PTR, _I64, _PTR, _PTR, _PTR]),
     "acx_bfs_window_partition": (_I32, [_PTR, _I64, _I64, _I64, _I64, _PTR, _PTR, _PTR, _I64, _PTR, _PTR, _I32, _PTR]),
     "acx_path_replay": (_I32, [_PTR, _PTR, _PTR, _I64, _I32, _I32, _I32, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR]),
     "acx_rows_features": (_I32, [_PTR, _I64, _I32, _PTR, _PTR]),
@@ -82,6 +83,7 @@ class EnvIO(ctypes.Structure):
 
 
 ENV_CERTIFIED, ENV_CHAINED, ENV_CHAIN_SLOTS = 1, 2, 4096
+MASK_SCAN_STATIC_MAX_N, MASK_SCAN_STATIC_BYTES = 1 << 22, 256 * 1024  # include/acx.h
 
 
 class AcxError(RuntimeError):

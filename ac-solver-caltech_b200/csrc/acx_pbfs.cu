@@ -472,6 +472,54 @@ extern "C" int64_t acx_bfs_mask_scan(const int32_t* mask, int64_t n, int64_t* ex
     return ACX_OK;
 }
 
+// ---- the same scan for callers that may not allocate (CUDA graph capture, serving loops) ------------------------
+// The cub scratch (tile descriptors of the one-pass scan) lives in a file-scope device array: every GPU that loads the
+// library holds ACX_MASK_SCAN_STATIC_BYTES until exit.  In host code the NAME of the array is a host-side stand-in,
+// not a device address; the address comes from cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) uint8_t g_mask_scan_scratch[ACX_MASK_SCAN_STATIC_BYTES];
+
+static int mask_scan_scratch(void** out) {
+    static void* addr[ACX_MAX_DEVICES] = {nullptr};
+    int dev = -1;
+    ACX_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= ACX_MAX_DEVICES) return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan_static: device %d out of range", dev);
+    if (!addr[dev]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_mask_scan_scratch);
+        if (e != cudaSuccess || !ptr)
+            return acx_fail(ACX_ERR_CUDA, "acx_bfs_mask_scan_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        addr[dev] = ptr;
+    }
+    *out = addr[dev];
+    return ACX_OK;
+}
+
+extern "C" int acx_bfs_mask_scan_static(const int32_t* mask, int64_t n, int64_t* excl_out, int64_t* total_out,
+                                        acx_stream_t stream) {
+    if (n < 0) return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan_static: n < 0");
+    if (n > ACX_MASK_SCAN_STATIC_MAX_N)
+        return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan_static: n = %lld is beyond the static scratch (at most %lld parents per call); "
+                        "use acx_bfs_mask_scan with caller scratch", (long long)n, (long long)ACX_MASK_SCAN_STATIC_MAX_N);
+    if (n == 0) return ACX_OK;
+    if (!mask || !excl_out || !total_out) return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan_static: null pointer");
+    cub::TransformInputIterator<int64_t, PopcountMask, const int32_t*> in(mask, PopcountMask());
+    size_t need = 0;
+    cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, need, in, excl_out, (int)n, (cudaStream_t)stream);
+    if (e != cudaSuccess) return acx_fail(ACX_ERR_CUDA, "cub::DeviceScan (size query): %s", cudaGetErrorString(e));
+    if (need > (size_t)ACX_MASK_SCAN_STATIC_BYTES)
+        return acx_fail(ACX_ERR_ARG, "acx_bfs_mask_scan_static: the scan wants %zu bytes of scratch, the static array has %d", need,
+                        (int)ACX_MASK_SCAN_STATIC_BYTES);
+    void* temp = nullptr;
+    if (int rc = mask_scan_scratch(&temp)) return rc;
+    // nothing to clear: the scan's own first kernel re-initialises every tile descriptor it is going to read
+    size_t tb = (size_t)ACX_MASK_SCAN_STATIC_BYTES;
+    e = cub::DeviceScan::ExclusiveSum(temp, tb, in, excl_out, (int)n, (cudaStream_t)stream);
+    if (e != cudaSuccess) return acx_fail(ACX_ERR_CUDA, "cub::DeviceScan: %s", cudaGetErrorString(e));
+    k_mask_total<<<1, 1, 0, (cudaStream_t)stream>>>(mask, excl_out, n, total_out);
+    ACX_CUDA(cudaGetLastError());
+    return ACX_OK;
+}
+
 namespace acx {
 // Group the local frontier of a level by round: window w = (gid - lo) / chunk.  Inside a window the order is free,
 // so a counting sort (histogram, scan on the host side, scatter) replaces a full sort.  Atomics are aggregated

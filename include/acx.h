@@ -293,6 +293,18 @@ int acx_pbfs_commit2(const uint64_t* recs, const int64_t* region_counts_dev, int
 int64_t acx_bfs_mask_scan(const int32_t* mask, int64_t n, int64_t* excl_out, int64_t* total_out, void* temp,
                           int64_t temp_bytes, acx_stream_t stream);
 
+/* acx_bfs_mask_scan without any allocation and without caller scratch.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same inputs, outputs and results as acx_bfs_mask_scan; the scan's scratch is a
+ * static device array of ACX_MASK_SCAN_STATIC_BYTES that every GPU which loads the library holds until exit.
+ * n > ACX_MASK_SCAN_STATIC_MAX_N is rejected (ACX_ERR_ARG, message in acx_last_error()).  The entry point calls no
+ * cudaMalloc / cudaFree / allocating routine.  All calls on a device share the one array, which keeps the last call's
+ * contents (nothing has to start at zero: the scan re-initialises what it reads): two calls that overlap on the GPU,
+ * e.g. on different streams, RACE -- order them on one stream or with events. */
+#define ACX_MASK_SCAN_STATIC_MAX_N (1 << 22)
+#define ACX_MASK_SCAN_STATIC_BYTES (256 * 1024)
+int acx_bfs_mask_scan_static(const int32_t* mask, int64_t n, int64_t* excl_out, int64_t* total_out, acx_stream_t stream);
+
 /* Group the local frontier of a level by round (window w = (gid - lo) / chunk of the global discovery ids; the
  * order inside a window is free): phase 0 counts[w] += 1; phase 1 scatters loc_out / gid_out to
  * offsets[w] + (running cursor[w]), offsets = exclusive scan of counts.  loc_out = first + index into gid. */
