@@ -38,9 +38,20 @@ class PlaneShard2(PlaneShard):
         cap = 12 * f + pad if G == 1 else min(12 * f + pad, int(12 * f / G * 1.15) + 8192 + pad)
         return (cap + 3) // 4 * 4
 
+    def __init__(self, m, cyclical, cap_local, max_parents, device, transport="auto"):
+        # acx_pbfs_probe3 appends a node the moment it claims a state: the round that the budget cuts may append up to
+        # 12 children per parent beyond the budget, and a reserved place whose claim lost its race can stay a hole
+        cap = int(cap_local) + 12 * int(max_parents) + int(cap_local) // 100 + (1 << 18)
+        super().__init__(m, cyclical, cap, max_parents, device, transport)
+
     def seed(self, root):
         super().seed(root)
         self.action[0] = 255  # the root was not discovered by a move
+
+    def probe(self, n_parents):
+        raise NotImplementedError("PlaneShard2 is driven by PlaneBFS (device-driven rounds)")
+
+    commit = probe
 
 
 def make_plane_shard(root, cyclical, cap_local, max_parents, device, transport="auto"):
@@ -87,7 +98,8 @@ class PlaneBFS(ShardedBFS):
         mask16 = [torch.zeros(c2, dtype=torch.int16, device=dev) for _ in range(2)]
         mask32 = [m.view(torch.int32) for m in mask16]
         mins = [torch.empty(2, dtype=torch.int64, device=dev) for _ in range(2)]
-        slot = [torch.empty(G * s.rcap, dtype=torch.int64, device=dev) for _ in range(2)]
+        starts = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(2)]  # n_local before / behind the round's probe
+        ends = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(2)]
         excl = torch.empty(C_max, dtype=torch.int32, device=dev)
         cursors = [torch.zeros(G + 1, dtype=torch.int64, device=dev) for _ in range(3)]
         allcs = [torch.empty(G * (G + 1), dtype=torch.int64, device=dev) for _ in range(3)]
@@ -161,7 +173,7 @@ class PlaneBFS(ShardedBFS):
                     if int(mirror[ring, 0]) != 0:
                         break
                 r2 = k % 2
-                buf, prev = recv[k % 3], recv[(k + 2) % 3]
+                buf = recv[k % 3]
                 counts, ready = pending
                 nxt = stage(k + 1, offs[i + 1], cuts[i + 1], cuts[i + 2]) if i + 1 < len(offs) else None
                 self._tick("expand_exchange")
@@ -173,8 +185,11 @@ class PlaneBFS(ShardedBFS):
                         main.wait_event(commit_ev[k - 2])  # slot / mask / mins of this ring position are free again
                 mask16[r2][: (C + 1) // 2 * 2].zero_()
                 mins[r2].fill_(SENT)
-                _lib.check(L.acx_pbfs_probe2(_ptr(buf), _ptr(prev), k & 1, rc_ptr, G + 1, G, s.rcap, _ptr(s.table), s.tcap, _ptr(s.nodes),
-                                             _ptr(slot[r2]), _ptr(mins[r2]), _ptr(mask32[r2]), _ptr(ctl), main.cuda_stream), "acx_pbfs_probe2")
+                starts[r2].copy_(s.n_local_dev)
+                _lib.check(L.acx_pbfs_probe3(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(s.table), s.tcap, _ptr(s.nodes), s.cap, _ptr(s.gid),
+                                             _ptr(s.n_local_dev), _ptr(starts[r2]), _ptr(mins[r2]), _ptr(mask32[r2]), _ptr(ctl),
+                                             main.cuda_stream), "acx_pbfs_probe3")
+                ends[r2].copy_(s.n_local_dev)
                 self._tick("probe")
                 probed = torch.cuda.Event()
                 probed.record(main)
@@ -196,9 +211,8 @@ class PlaneBFS(ShardedBFS):
                     if rcd:
                         _lib.check(rcd, "acx_pbfs_decide")
                     self._tick("reduce_scan_decide")
-                    _lib.check(L.acx_pbfs_commit2(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(slot[r2]), _ptr(excl), _ptr(mask32[r2]), off,
-                                                  _ptr(ctl), _ptr(s.n_local_dev), _ptr(s.table), _ptr(s.nodes), _ptr(s.gid), _ptr(s.parent),
-                                                  _ptr(s.action), cs), "acx_pbfs_commit2")
+                    _lib.check(L.acx_pbfs_commit3(_ptr(starts[r2]), _ptr(ends[r2]), G * s.rcap, s.cap, _ptr(excl), _ptr(mask32[r2]), off,
+                                                  _ptr(ctl), _ptr(s.gid), _ptr(s.parent), _ptr(s.action), cs), "acx_pbfs_commit3")
                     self._tick("commit")
                     commit_ev[k] = torch.cuda.Event()
                     commit_ev[k].record(st_commit)
@@ -217,7 +231,7 @@ class PlaneBFS(ShardedBFS):
             n_local = c[16]
             self.n_nodes, self.n_expanded = c[1], c[2]
             if c[6]:
-                raise RuntimeError("plane bfs: a send region overflowed (hash imbalance above the 15% head room)")
+                raise RuntimeError("plane bfs: a send region or the node store overflowed (hash imbalance above the head room)")
             self.n_candidates, self.comm_bytes = c[8], 32 * (c[8] - c[9])
             if c[0]:
                 if c[0] == STOP_SOLVED:

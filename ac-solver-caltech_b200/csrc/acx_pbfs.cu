@@ -554,9 +554,11 @@ __global__ void __launch_bounds__(256) k_win_part(const int64_t* gid, int64_t n,
         g[k] = 0;
         if (i < n) {
             g[k] = gid[i];
-            w[k] = (int)((g[k] - lo) / chunk);
-            mn = min(mn, w[k]);
-            mx = max(mx, w[k]);
+            if (g[k] >= lo) {  // gid -1: a hole of the node store (acx_pbfs_probe3), not a node
+                w[k] = (int)((g[k] - lo) / chunk);
+                mn = min(mn, w[k]);
+                mx = max(mx, w[k]);
+            }
         }
     }
     if (mx >= 0) {

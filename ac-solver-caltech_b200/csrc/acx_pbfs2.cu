@@ -9,13 +9,18 @@
 //                    per lane (round 1: 380 GB/s of the 900 GB/s egress).  A run is padded to four records with null
 //                    records so that every run starts on a line.  The child that undoes the move which discovered the
 //                    parent is its grandparent (cyclical = 0: the 12 moves are pairwise inverse) and is not sent.
-//   k_pbfs_probe2    visited-set probe with the winner resolution FUSED in: a candidate sets its bit in the per-parent
-//                    mask BEFORE it claims a slot (and clears it if the claim fails); a candidate of lower order that
-//                    replaces a claim clears the loser's bit.  No separate resolve pass over the records and the table.
+//   k_pbfs_probe3    visited-set probe in which a claim is FINAL: the candidate reserves its place in the node store
+//                    first and claims the table slot with that place, so the slot is written once in its life (the machine
+//                    serves 36 G random memory operations / s, reads and writes alike: tools/random_access.cu -- the first
+//                    version wrote the slot twice, provisional claim and node id).  Which of the equal candidates of a
+//                    round discovered the state first is settled beside the node (atomicMin of the order, in gid[]), and
+//                    the per-parent mask follows by XOR.
 //   k_pbfs_decide    after the masks are all-reduced: exclusive scan of the new-node counts, then ONE thread replays the
 //                    reference's decision for the round (first success / error by order, the budget cut of
 //                    breadth_first.py:91-95) into a control block in device memory.
-//   k_pbfs_commit2   winners become nodes unless the control block says the search stopped in this round.
+//   k_pbfs_commit3   the nodes of the round get their global id, parent and action from the winning order -- a
+//                    streaming pass over the round's part of the node store -- unless the control block says the search
+//                    stopped in this round.
 // Every kernel returns at once when the control block holds a stop code, so the host enqueues whole levels without
 // reading anything back and looks at the control block once per level.
 #include <cuda_runtime.h>
@@ -66,7 +71,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_pbfs_expand2(const uint64_t* __r
     const bool cyc = cyclical != 0;
     for (int64_t k0 = (int64_t)blockIdx.x * EX_THREADS; k0 < f; k0 += (int64_t)gridDim.x * EX_THREADS) {
         const int64_t k = k0 + tid;
-        const bool active = k < f;
+        const bool active = k < f && gids[k] >= 0;  // gid -1: a hole of the node store (acx_pbfs_probe3), not a node
         R64 r[2];
         r[0].S = r[0].T = r[1].S = r[1].T = 0ull;
         r[0].n = r[1].n = 1;
@@ -188,123 +193,175 @@ __global__ void __launch_bounds__(EX_THREADS) k_pbfs_expand2(const uint64_t* __r
     }
 }
 
-struct Pb2Params {
-    const uint64_t* recs_prev;    // the records of the previous round (its claims may still be provisional in the table)
-    uint64_t parity;              // of this round: provisional entries carry it in bit 46 of the value
+struct Pb3Params {
     const uint64_t* recs;         // nreg regions of rcap records
     const int64_t* region_counts; // device: records (incl. null padding) in region s = region_counts[s * count_stride]
     int64_t count_stride;
     int nreg;
     int64_t rcap;
-    uint64_t* table;
+    uint64_t* table;              // slot = tag(16) | place of the node in the local store (48)
     int64_t tcap;
-    const uint64_t* nodes;
-    int64_t* slot;
+    uint64_t* nodes;
+    int64_t node_cap;
+    unsigned long long* gid;      // during the round: PB_IN_ROUND | smallest order seen for the node; -1 = never used
+    unsigned long long* n_local;
+    const int64_t* round_start;   // device: n_local before this round's probe
+    const int64_t* round_end;     // device: n_local behind it (commit)
     unsigned long long* mins;
-    unsigned* mask32;  // 16 bits per parent, two parents per word
+    unsigned* mask32;             // 16 bits per parent, two parents per word
     const int32_t* excl;
     int64_t parent_base;
     int64_t* ctl;
-    unsigned long long* n_local;
-    uint64_t* nodes_w;
-    int64_t* gid;
     int64_t* parent;
     uint8_t* action;
 };
 
-__device__ __forceinline__ void mask_set(unsigned* mask32, int64_t ord) {
+static constexpr unsigned long long PB_IN_ROUND = 1ull << 62;  // keeps the orders of a round apart from real global ids
+static constexpr uint64_t PB_PLACE = (1ull << 48) - 1;
+
+// The winner mask is kept with XOR: a candidate toggles its own bit when it becomes the node's smallest order, and
+// toggles the bit of the order it displaced.  A bit is toggled at most once by its owner and at most once by its
+// displacer, and XOR commutes: when the kernel ends bit (p, a) is set exactly for the first discovery of every new
+// state, whatever order the toggles became visible in -- no fence anywhere in the probe.
+__device__ __forceinline__ void mask_flip(unsigned* mask32, int64_t ord) {
     const int64_t p = ord / 12;
-    atomicOr(mask32 + (p >> 1), (1u << (int)(ord % 12)) << (16 * (int)(p & 1)));
-}
-__device__ __forceinline__ void mask_clear(unsigned* mask32, int64_t ord) {
-    const int64_t p = ord / 12;
-    atomicAnd(mask32 + (p >> 1), ~((1u << (int)(ord % 12)) << (16 * (int)(p & 1))));
+    atomicXor(mask32 + (p >> 1), (1u << (int)(ord % 12)) << (16 * (int)(p & 1)));
 }
 
-// Table slot = tag(16) | PROV(1) | value(47): value = node id, or (PROV) the index of the candidate that currently
-// claims the state in this round.  slot[j] >= 0 and the mask bit of j are set exactly for the claim holders when the
-// kernel ends: the first discovery (smallest order) of every new state.
-template <int MINB>
-__global__ void __launch_bounds__(256, MINB) k_pbfs_probe2(const Pb2Params p) {
-    if (p.ctl[CTL_STOP] != 0) return;
-    const int64_t s = blockIdx.y, i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // region, record in the region
-    if (i >= p.region_counts[s * p.count_stride]) return;
-    const int64_t j = s * p.rcap + i;
-    const PWords rec = pb_load(p.recs + 4 * j);
-    if ((rec.w[0] | rec.w[1]) == 0ull) {  // null record (run padding)
-        p.slot[j] = -3;
-        return;
+__device__ __forceinline__ void settle_order(const Pb3Params& p, int64_t place, int64_t ord) {
+    const unsigned long long mine = PB_IN_ROUND | (unsigned long long)ord;
+    const unsigned long long old = atomicMin(p.gid + place, mine);
+    if (old > mine) {
+        mask_flip(p.mask32, ord);
+        if (old != ~0ull) mask_flip(p.mask32, (int64_t)(old & ~PB_IN_ROUND));
     }
-    const int64_t ord = pb_order(rec);
-    if (pb_status(rec)) {
-        atomicMin(p.mins + 1, (unsigned long long)ord);
-        p.slot[j] = -2;
-        return;
-    }
-    if (pb_total(rec) == 2) {  // breadth_first.py:84-85, tested before the visited set
-        atomicMin(p.mins, (unsigned long long)ord);
-        p.slot[j] = -2;
-        return;
-    }
-    const PWords st = pb_state(rec);
-    const uint64_t h = pb_hash(st);
-    const uint64_t tag = ((h >> 48) | 1ull) << 48;
-    const uint64_t mine = tag | PB_PROV | (p.parity << 46) | (uint64_t)j;
-    const uint64_t mask = (uint64_t)p.tcap - 1;
-    uint64_t slot = (h ^ (h >> 23)) & mask;
+}
+
+// Walk the probe sequence of one candidate from `slot` (whose content `e` is already loaded).  Returns true when the
+// candidate is settled (claimed its node, or met an equal state), false when it stands at an EMPTY slot and holds no
+// place to claim it with (`spare` < 0): the caller reserves one and calls again.
+__device__ __forceinline__ bool probe_walk(const Pb3Params& p, const PWords& st, int64_t ord, uint64_t tag, uint64_t tmask, int64_t rs,
+                                           uint64_t& slot, uint64_t& e, int64_t& spare) {
     for (;;) {
-        uint64_t e = __ldcg(p.table + slot);
         if (e == 0ull) {
-            // tentative winner first, claim second: whoever replaces the claim later finds both in place
-            mask_set(p.mask32, ord);
-            p.slot[j] = (int64_t)slot;
-            __threadfence();
-            const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(p.table + slot), 0ull, (unsigned long long)mine);
-            if (old == 0ull) return;
-            mask_clear(p.mask32, ord);  // nobody saw the claim: undo
+            if (spare < 0) return false;
+            const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(p.table + slot), 0ull, (unsigned long long)(tag | (uint64_t)spare));
+            if (old == 0ull) {  // the state is new and this is its node, for good
+                pb_store(p.nodes + 4 * spare, st);
+                settle_order(p, spare, ord);
+                spare = -1;
+                return true;
+            }
             e = old;
         }
         if ((e >> 48) == (tag >> 48)) {
-            if ((e & PB_PROV) && ((e >> 46) & 1ull) != p.parity) {
-                // a claim of the PREVIOUS round that its commit (running next to this probe) has not turned into a node
-                // yet: every candidate of that round precedes this one in the reference's order, so an equal state is visited
-                const PWords orec = pb_load(p.recs_prev + 4 * (int64_t)(e & PB_IDX));
-                if (pb_equal(st, pb_state(orec))) {
-                    p.slot[j] = -1;
-                    return;
+            const int64_t place = (int64_t)(e & PB_PLACE);
+            PWords nd = pb_load_cg(p.nodes + 4 * place);
+            if (place >= rs) {  // claimed in this round: its owner may be between the claim and the store
+                while (nd.w[0] == 0ull) {
+                    __nanosleep(32);
+                    nd = pb_load_cg(p.nodes + 4 * place);
                 }
-            } else if (e & PB_PROV) {
-                for (;;) {
-                    const int64_t other = (int64_t)(e & PB_IDX);
-                    const PWords orec = pb_load(p.recs + 4 * other);
-                    if (!pb_equal(st, pb_state(orec))) break;
-                    const int64_t oord = pb_order(orec);
-                    if (oord < ord) {  // a duplicate inside the round, discovered earlier in the reference's order
-                        p.slot[j] = -1;
-                        return;
-                    }
-                    mask_set(p.mask32, ord);
-                    p.slot[j] = (int64_t)slot;
-                    __threadfence();
-                    const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(p.table + slot), (unsigned long long)e,
-                                                   (unsigned long long)mine);
-                    if (old == e) {  // the claim is mine now: the loser's bit and slot go
-                        mask_clear(p.mask32, oord);
-                        p.slot[other] = -1;
-                        return;
-                    }
-                    mask_clear(p.mask32, ord);
-                    e = old;  // somebody else replaced it first: look again
-                }
-            } else {
-                const int64_t id = (int64_t)(e & PB_VAL);
-                if (pb_equal(st, pb_load_cg(p.nodes + 4 * id))) {  // the previous round's commit may be appending nodes right now
-                    p.slot[j] = -1;
-                    return;
+            }
+            if (pb_equal(st, nd)) {
+                // visited -- or discovered earlier in this very round: the smaller order is the reference's first discovery
+                if (place >= rs) settle_order(p, place, ord);
+                return true;
+            }
+        }
+        slot = (slot + 1) & tmask;
+        e = __ldcg(p.table + slot);
+    }
+}
+
+// Persistent grid: a thread walks over the records of its region with a stride.  Places in the node store are handed
+// out where the CTA is converged, to exactly the lanes that stand at an empty slot without a place, from a pool the CTA
+// refills with ONE atomic on the store's counter for several iterations at a time (every atomic on that one address
+// costs about ten cycles in L2 and they serialize: with one per warp and iteration the counter alone set the kernel's
+// duration).  A place whose claim then lost its race (an equal candidate claimed the slot first) is kept for the thread's
+// next claim; what a thread or the pool still holds at the end stays a hole in the node store (gid -1, never expanded;
+// the refills shrink to the exact need in the CTA's last iterations).
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) k_pbfs_probe3(const Pb3Params p) {
+    if (p.ctl[CTL_STOP] != 0) return;
+    __shared__ int s_wneed[8];
+    __shared__ long long s_range[4];  // old pool base, places taken from it, new chunk base
+    __shared__ long long s_pool[2];   // base, left
+    const int64_t s = blockIdx.y;  // region
+    const int64_t cnt = p.region_counts[s * p.count_stride];
+    const int64_t T = (int64_t)gridDim.x * 256;
+    const int64_t rs = *p.round_start;
+    const uint64_t* recs = p.recs + 4 * s * p.rcap;
+    const uint64_t tmask = (uint64_t)p.tcap - 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int64_t spare = -1;
+    if (threadIdx.x == 0) s_pool[0] = s_pool[1] = 0;
+    for (int64_t base = (int64_t)blockIdx.x * 256; base < cnt; base += T) {  // block-uniform: the CTA meets at the barriers
+        const int64_t i = base + threadIdx.x;
+        bool live = false, settled = true;
+        PWords st;
+        st.w[0] = st.w[1] = st.w[2] = st.w[3] = 0ull;
+        int64_t ord = 0;
+        uint64_t tag = 0, slot = 0, e = 0;
+        if (i < cnt) {
+            const PWords rec = pb_load(recs + 4 * i);
+            if ((rec.w[0] | rec.w[1]) != 0ull) {  // not a null record (run padding)
+                ord = pb_order(rec);
+                if (pb_status(rec)) {
+                    atomicMin(p.mins + 1, (unsigned long long)ord);
+                } else if (pb_total(rec) == 2) {  // breadth_first.py:84-85, tested before the visited set
+                    atomicMin(p.mins, (unsigned long long)ord);
+                } else {
+                    live = true;
+                    st = pb_state(rec);
+                    const uint64_t h = pb_hash(st);
+                    tag = ((h >> 48) | 1ull) << 48;
+                    slot = (h ^ (h >> 23)) & tmask;
+                    e = __ldcg(p.table + slot);
                 }
             }
         }
-        slot = (slot + 1) & mask;
+        if (live) settled = probe_walk(p, st, ord, tag, tmask, rs, slot, e, spare);
+        const unsigned need = __ballot_sync(0xFFFFFFFFu, !settled);
+        if (lane == 0) s_wneed[warp] = __popc(need);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int total = 0;
+            for (int w = 0; w < 8; ++w) {
+                const int c = s_wneed[w];
+                s_wneed[w] = total;
+                total += c;
+            }
+            long long pb = s_pool[0], left = s_pool[1];
+            s_range[0] = pb;
+            if (left >= total) {
+                s_range[1] = total;
+                s_range[2] = 0;
+                s_pool[0] = pb + total;
+                s_pool[1] = left - total;
+            } else {  // the pool runs dry: what it holds goes first, the rest comes from a new chunk
+                const int64_t iters_left = (cnt - base + T - 1) / T;  // this one included
+                const long long mult = iters_left - 1 > 8 ? 8 : (iters_left - 1 < 1 ? 1 : iters_left - 1);
+                const long long want = (long long)(total - left) + (mult - 1) * total;
+                const long long nb = (long long)atomicAdd(p.n_local, (unsigned long long)want);
+                s_range[1] = left;
+                s_range[2] = nb;
+                s_pool[0] = nb + (total - left);
+                s_pool[1] = want - (total - left);
+            }
+        }
+        __syncthreads();
+        if (!settled) {
+            const long long r = s_wneed[warp] + __popc(need & ((1u << lane) - 1u));
+            spare = r < s_range[1] ? s_range[0] + r : s_range[2] + (r - s_range[1]);
+            if (spare >= p.node_cap) {  // the node store is full: the host raises
+                p.ctl[CTL_OVERFLOW] = 1;
+                spare = -1;
+            } else {
+                probe_walk(p, st, ord, tag, tmask, rs, slot, e, spare);
+            }
+        }
+        __syncthreads();  // s_wneed / s_range are rewritten in the next iteration
     }
 }
 
@@ -380,29 +437,20 @@ __global__ void k_pbfs_decide(const uint16_t* mask16, const int32_t* excl, int64
     }
 }
 
-__global__ void __launch_bounds__(256) k_pbfs_commit2(const Pb2Params p) {
+// the nodes the probe appended in this round: order -> (global id, parent, action)
+__global__ void __launch_bounds__(256) k_pbfs_commit3(const Pb3Params p) {
     if (p.ctl[CTL_STOP] != 0) return;
-    const int64_t s = blockIdx.y, i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // region, record in the region
-    if (i >= p.region_counts[s * p.count_stride]) return;
-    const int64_t j = s * p.rcap + i;
-    const int64_t sl = p.slot[j];
-    if (sl < 0) return;
-    const PWords rec = pb_load(p.recs + 4 * j);
-    const int64_t ord = pb_order(rec);
+    const int64_t place = *p.round_start + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (place >= *p.round_end || place >= p.node_cap) return;
+    const unsigned long long o = p.gid[place];
+    if (o == ~0ull) return;  // a hole: reserved, never claimed
+    const int64_t ord = (int64_t)(o & ~PB_IN_ROUND);
     const int64_t par = ord / 12;
     const int act = (int)(ord % 12);
     const unsigned m16 = (p.mask32[par >> 1] >> (16 * (int)(par & 1))) & 0xFFFFu;
-    const int64_t gid = p.ctl[CTL_GID_BASE] + p.excl[par] + __popc(m16 & ((1u << act) - 1u));
-    const int64_t id = (int64_t)atomicAdd(p.n_local, 1ull);
-    const PWords st = pb_state(rec);
-    pb_store(p.nodes_w + 4 * id, st);
-    p.gid[id] = gid;
-    p.parent[id] = p.parent_base + par;
-    p.action[id] = (uint8_t)act;
-    // the probe of the next round may run next to this kernel: the node must be visible before the slot names it
-    __threadfence();
-    // the slot keeps its tag (recomputed from the state: no read of the random table line) and now names the node
-    __stcg(p.table + sl, (((pb_hash(st) >> 48) | 1ull) << 48) | (uint64_t)id);
+    p.gid[place] = (unsigned long long)(p.ctl[CTL_GID_BASE] + p.excl[par] + __popc(m16 & ((1u << act) - 1u)));
+    p.parent[place] = p.parent_base + par;
+    p.action[place] = (uint8_t)act;
 }
 
 }  // namespace acx
@@ -444,38 +492,35 @@ extern "C" int acx_pbfs_expand2(const uint64_t* nodes, const uint8_t* action, co
     return ACX_OK;
 }
 
-static int pb2_common(Pb2Params& p, const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions,
-                      int64_t region_cap, const char* who) {
+extern "C" int acx_pbfs_probe3(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap,
+                               uint64_t* table, int64_t tcap, uint64_t* nodes, int64_t node_cap, int64_t* gid, uint64_t* n_local,
+                               const int64_t* round_start_dev, uint64_t* mins, uint32_t* mask32, int64_t* ctl, acx_stream_t stream) {
+    if (tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe3: table capacity must be a power of two");
     if (!recs || !region_counts_dev || count_stride < 1 || n_regions < 1 || n_regions > PB_MAX_WORLD || region_cap < 1)
-        return acx_fail(ACX_ERR_ARG, "%s: need records, device region counts, 1 <= n_regions <= 32", who);
-    p.recs = recs;
-    p.region_counts = region_counts_dev;
-    p.count_stride = count_stride;
-    p.nreg = n_regions;
-    p.rcap = region_cap;
-    return ACX_OK;
-}
-
-extern "C" int acx_pbfs_probe2(const uint64_t* recs, const uint64_t* recs_prev, int parity, const int64_t* region_counts_dev,
-                               int64_t count_stride, int n_regions, int64_t region_cap, uint64_t* table, int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins,
-                               uint32_t* mask32, const int64_t* ctl, acx_stream_t stream) {
-    if (tcap < 2 || (tcap & (tcap - 1))) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe2: table capacity must be a power of two");
-    Pb2Params p = {};
-    if (int rc = pb2_common(p, recs, region_counts_dev, count_stride, n_regions, region_cap, "acx_pbfs_probe2")) return rc;
-    if (!table || !nodes || !slot || !mins || !mask32 || !ctl || !recs_prev) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe2: null pointer");
-    if ((int64_t)n_regions * region_cap > (int64_t)PB_IDX) return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe2: too many records per round");
-    p.recs_prev = recs_prev;
-    p.parity = (uint64_t)(parity & 1);
-    p.table = table; p.tcap = tcap; p.nodes = nodes; p.slot = slot;
-    p.mins = reinterpret_cast<unsigned long long*>(mins); p.mask32 = mask32; p.ctl = const_cast<int64_t*>(ctl);
-    const dim3 grid((unsigned)((region_cap + 255) / 256), (unsigned)n_regions);
-    static const int occ = [] {  // ACX_PROBE_OCC=5|6|8 resident CTAs per SM (registers 44 / 40 / 32): tuning knob
+        return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe3: need records, device region counts, 1 <= n_regions <= 32");
+    if (!table || !nodes || !gid || !n_local || !round_start_dev || !mins || !mask32 || !ctl || node_cap < 1)
+        return acx_fail(ACX_ERR_ARG, "acx_pbfs_probe3: null pointer");
+    Pb3Params p = {};
+    p.recs = recs; p.region_counts = region_counts_dev; p.count_stride = count_stride; p.nreg = n_regions; p.rcap = region_cap;
+    p.table = table; p.tcap = tcap; p.nodes = nodes; p.node_cap = node_cap; p.gid = reinterpret_cast<unsigned long long*>(gid);
+    p.n_local = reinterpret_cast<unsigned long long*>(n_local); p.round_start = round_start_dev;
+    p.mins = reinterpret_cast<unsigned long long*>(mins); p.mask32 = mask32; p.ctl = ctl;
+    static const int occ = [] {  // ACX_PROBE_OCC=2..8 resident CTAs per SM: tuning knob
         const char* e = getenv("ACX_PROBE_OCC");
-        return e ? atoi(e) : 6;
+        return e ? atoi(e) : 8;
     }();
-    if (occ >= 8) k_pbfs_probe2<8><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
-    else if (occ == 6) k_pbfs_probe2<6><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
-    else k_pbfs_probe2<5><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int per_sm = occ >= 8 ? 8 : (occ >= 6 ? 6 : (occ >= 4 ? 4 : 2));
+    // persistent: the resident CTAs of the device, split over the regions (their record counts are near equal)
+    int64_t gx = ((int64_t)sms * per_sm + n_regions - 1) / n_regions;
+    if (gx > (region_cap + 255) / 256) gx = (region_cap + 255) / 256;
+    const dim3 grid((unsigned)gx, (unsigned)n_regions);
+    if (per_sm == 8) k_pbfs_probe3<8><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else if (per_sm == 6) k_pbfs_probe3<6><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else if (per_sm == 4) k_pbfs_probe3<4><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else k_pbfs_probe3<2><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }
@@ -502,19 +547,16 @@ extern "C" int64_t acx_pbfs_decide(const uint16_t* mask16, int32_t* excl_out, in
     return ACX_OK;
 }
 
-extern "C" int acx_pbfs_commit2(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap,
-                                const int64_t* slot, const int32_t* excl, const uint32_t* mask32, int64_t parent_base,
-                                const int64_t* ctl, uint64_t* n_local, uint64_t* table, uint64_t* nodes, int64_t* gid,
+extern "C" int acx_pbfs_commit3(const int64_t* round_start_dev, const int64_t* round_end_dev, int64_t max_new, int64_t node_cap,
+                                const int32_t* excl, const uint32_t* mask32, int64_t parent_base, const int64_t* ctl, int64_t* gid,
                                 int64_t* parent, uint8_t* action, acx_stream_t stream) {
-    Pb2Params p = {};
-    if (int rc = pb2_common(p, recs, region_counts_dev, count_stride, n_regions, region_cap, "acx_pbfs_commit2")) return rc;
-    if (!slot || !excl || !mask32 || !ctl || !n_local || !table || !nodes || !gid || !parent || !action)
-        return acx_fail(ACX_ERR_ARG, "acx_pbfs_commit2: null pointer");
-    p.slot = const_cast<int64_t*>(slot); p.excl = excl; p.mask32 = const_cast<unsigned*>(mask32); p.parent_base = parent_base;
-    p.ctl = const_cast<int64_t*>(ctl); p.n_local = reinterpret_cast<unsigned long long*>(n_local); p.table = table;
-    p.nodes_w = nodes; p.gid = gid; p.parent = parent; p.action = action;
-    const dim3 grid((unsigned)((region_cap + 255) / 256), (unsigned)n_regions);
-    k_pbfs_commit2<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    if (!round_start_dev || !round_end_dev || !excl || !mask32 || !ctl || !gid || !parent || !action || max_new < 1 || node_cap < 1)
+        return acx_fail(ACX_ERR_ARG, "acx_pbfs_commit3: bad argument");
+    Pb3Params p = {};
+    p.round_start = round_start_dev; p.round_end = round_end_dev; p.node_cap = node_cap;
+    p.excl = excl; p.mask32 = const_cast<unsigned*>(mask32); p.parent_base = parent_base;
+    p.ctl = const_cast<int64_t*>(ctl); p.gid = reinterpret_cast<unsigned long long*>(gid); p.parent = parent; p.action = action;
+    k_pbfs_commit3<<<(unsigned)((max_new + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }

@@ -262,30 +262,34 @@ int acx_pbfs_commit(const uint64_t* recs, const int64_t* region_counts, int n_re
  *                     contiguous runs padded to 4 records (128 bytes) with null records (region_cap % 4 == 0, regions
  *                     128-byte aligned); with cyclical == 0 the child that undoes the move `action[parent]` (the
  *                     grandparent; 255 = no such move) is not sent.  cursor[o] counts records incl. padding.
- *   acx_pbfs_probe2   region counts are a DEVICE array; the winner resolution is fused in: mask32 (uint32 view of one
- *                     uint16 per parent, caller zeroes) has bit a of parent p set iff child (p, a) is the first discovery
- *                     of a new state, slot[j] >= 0 exactly for those candidates; mins = {min success order, min error
- *                     order} (caller sets both to 2^62).  `parity` (round number & 1) tags the provisional entries of
- *                     this round; an entry of the other parity belongs to the previous round, whose records are still
- *                     at recs_prev and whose commit may run NEXT TO this probe: an equal state there is visited
- *                     (every candidate of an earlier round precedes this one in the reference's order).
+ *   acx_pbfs_probe3   region counts are a DEVICE array.  A claim is final: the candidate first reserves a place in the
+ *                     node store (n_local, one atomic per warp), then claims the empty table slot with tag | place and
+ *                     writes its state to nodes[place] -- the slot is never written again.  Equal candidates of one round
+ *                     settle the reference's first discovery beside the node: gid[place] (caller: -1 beyond n_local) holds
+ *                     2^62 | the smallest order until the commit, and mask32 (uint32 view of one uint16 per parent, caller
+ *                     zeroes) ends with bit a of parent p set iff child (p, a) is the first discovery of a new state.
+ *                     round_start_dev = n_local before the call (a place at or beyond it belongs to this round); a place
+ *                     of an earlier round is a visited state whether or not its commit has run, so this probe may run
+ *                     next to the previous round's commit.  mins = {min success order, min error order} (caller sets
+ *                     both to 2^62).  A reserved place whose claim lost its race is reused by the same thread; what is
+ *                     left over stays a hole (gid -1, zero node): acx_pbfs_expand2 and acx_bfs_window_partition skip it.
+ *                     A full node store sets ctl[6].
  *   acx_pbfs_decide   exclusive scan of popcount(mask16) -> excl_out (int32), then the decision of the round
  *                     (breadth_first.py:84-95 in the reference's order) into ctl.  temp == NULL returns the scratch size.
- *   acx_pbfs_commit2  claim holders become nodes with global id ctl[3] + excl[p] + popcount(mask16[p] & bits below a). */
+ *   acx_pbfs_commit3  the places [round_start, round_end) get global id ctl[3] + excl[p] + popcount(mask16[p] & bits below a),
+ *                     parent and action from their winning order (p, a); max_new bounds round_end - round_start. */
 int acx_pbfs_expand2(const uint64_t* nodes, const uint8_t* action, const int64_t* loc, const int64_t* gids, int64_t ord_base,
                      int64_t f, int m, int cyclical, int world, int64_t region_cap, uint64_t* cursor,
                      uint8_t* const* dst_regions, const int64_t* ctl, acx_stream_t stream);
-int acx_pbfs_probe2(const uint64_t* recs, const uint64_t* recs_prev, int parity, const int64_t* region_counts_dev, int64_t count_stride,
-                    int n_regions, int64_t region_cap, uint64_t* table,
-                    int64_t tcap, const uint64_t* nodes, int64_t* slot, uint64_t* mins, uint32_t* mask32, const int64_t* ctl,
-                    acx_stream_t stream);
+int acx_pbfs_probe3(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap,
+                    uint64_t* table, int64_t tcap, uint64_t* nodes, int64_t node_cap, int64_t* gid, uint64_t* n_local,
+                    const int64_t* round_start_dev, uint64_t* mins, uint32_t* mask32, int64_t* ctl, acx_stream_t stream);
 int64_t acx_pbfs_decide(const uint16_t* mask16, int32_t* excl_out, int64_t n_parents, const uint64_t* mins, int64_t parent_base,
                         int64_t budget, int64_t* ctl, const int64_t* counts, int world, int rank, void* temp, int64_t temp_bytes,
                         acx_stream_t stream);
-int acx_pbfs_commit2(const uint64_t* recs, const int64_t* region_counts_dev, int64_t count_stride, int n_regions, int64_t region_cap,
-                     const int64_t* slot, const int32_t* excl, const uint32_t* mask32, int64_t parent_base, const int64_t* ctl,
-                     uint64_t* n_local, uint64_t* table, uint64_t* nodes, int64_t* gid, int64_t* parent, uint8_t* action,
-                     acx_stream_t stream);
+int acx_pbfs_commit3(const int64_t* round_start_dev, const int64_t* round_end_dev, int64_t max_new, int64_t node_cap,
+                     const int32_t* excl, const uint32_t* mask32, int64_t parent_base, const int64_t* ctl, int64_t* gid,
+                     int64_t* parent, uint8_t* action, acx_stream_t stream);
 
 /* Exclusive scan of popcount(mask[p]) over the parents of a round: excl_out[p] = new nodes discovered by the
  * parents before p (reference order), total_out[0] = new nodes of the round.  temp == NULL returns the scratch
