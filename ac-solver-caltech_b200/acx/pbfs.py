@@ -40,8 +40,9 @@ class PlaneShard2(PlaneShard):
 
     def __init__(self, m, cyclical, cap_local, max_parents, device, transport="auto"):
         # acx_pbfs_probe3 appends a node the moment it claims a state: the round that the budget cuts may append up to
-        # 12 children per parent beyond the budget, and a reserved place whose claim lost its race can stay a hole
-        cap = int(cap_local) + 12 * int(max_parents) + int(cap_local) // 100 + (1 << 18)
+        # 12 children per parent beyond the budget, and so may the round behind it (its probe runs next to the decision
+        # of the round that stops the search); a reserved place whose claim lost its race can stay a hole
+        cap = int(cap_local) + 24 * int(max_parents) + 3 * int(cap_local) // 100 + (1 << 18)  # holes: 1.4 % measured from AK(3)
         super().__init__(m, cyclical, cap, max_parents, device, transport)
 
     def seed(self, root):

@@ -54,7 +54,8 @@ static constexpr int EX_SLOTS = EX_THREADS * EX_GM + 4 * PB_MAX_WORLD;  // stage
 // inverse of move a (ac_moves.py:188-206): 0<->2, 1<->3 (r_i r_j^{+-1}); 4<->8, 5<->9, 6<->10, 7<->11 (g <-> g^-1)
 __device__ __forceinline__ int pb_inverse_move(int a) { return a < 4 ? (a ^ 2) : (a < 8 ? a + 4 : a - 4); }
 
-__global__ void __launch_bounds__(EX_THREADS) k_pbfs_expand2(const uint64_t* __restrict__ nodes, const uint8_t* __restrict__ action,
+template <int MINB>
+__global__ void __launch_bounds__(EX_THREADS, MINB) k_pbfs_expand2(const uint64_t* __restrict__ nodes, const uint8_t* __restrict__ action,
                                                             const int64_t* __restrict__ loc, const int64_t* __restrict__ gids,
                                                             int64_t ord_base, int64_t f, int m, int cyclical, int world,
                                                             int64_t region_cap, unsigned long long* cursor, const PbDst2 dst,
@@ -224,6 +225,11 @@ static constexpr uint64_t PB_PLACE = (1ull << 48) - 1;
 // displacer, and XOR commutes: when the kernel ends bit (p, a) is set exactly for the first discovery of every new
 // state, whatever order the toggles became visible in -- no fence anywhere in the probe.
 __device__ __forceinline__ void mask_flip(unsigned* mask32, int64_t ord) {
+    if (((uint64_t)ord >> 32) == 0ull) {  // every round of less than 2^32 / 12 parents: a 32-bit division (the 64-bit one was a third of the kernel's instructions)
+        const uint32_t o = (uint32_t)ord, p = o / 12u, a = o - 12u * p;
+        atomicXor(mask32 + (p >> 1), (1u << a) << (16u * (p & 1u)));
+        return;
+    }
     const int64_t p = ord / 12;
     atomicXor(mask32 + (p >> 1), (1u << (int)(ord % 12)) << (16 * (int)(p & 1)));
 }
@@ -281,22 +287,22 @@ __device__ __forceinline__ bool probe_walk(const Pb3Params& p, const PWords& st,
 // duration).  A place whose claim then lost its race (an equal candidate claimed the slot first) is kept for the thread's
 // next claim; what a thread or the pool still holds at the end stays a hole in the node store (gid -1, never expanded;
 // the refills shrink to the exact need in the CTA's last iterations).
-template <int MINB>
-__global__ void __launch_bounds__(256, MINB) k_pbfs_probe3(const Pb3Params p) {
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB) k_pbfs_probe3(const Pb3Params p) {
     if (p.ctl[CTL_STOP] != 0) return;
-    __shared__ int s_wneed[8];
+    __shared__ int s_wneed[NT / 32];
     __shared__ long long s_range[4];  // old pool base, places taken from it, new chunk base
     __shared__ long long s_pool[2];   // base, left
     const int64_t s = blockIdx.y;  // region
     const int64_t cnt = p.region_counts[s * p.count_stride];
-    const int64_t T = (int64_t)gridDim.x * 256;
+    const int64_t T = (int64_t)gridDim.x * NT;
     const int64_t rs = *p.round_start;
     const uint64_t* recs = p.recs + 4 * s * p.rcap;
     const uint64_t tmask = (uint64_t)p.tcap - 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int64_t spare = -1;
     if (threadIdx.x == 0) s_pool[0] = s_pool[1] = 0;
-    for (int64_t base = (int64_t)blockIdx.x * 256; base < cnt; base += T) {  // block-uniform: the CTA meets at the barriers
+    for (int64_t base = (int64_t)blockIdx.x * NT; base < cnt; base += T) {  // block-uniform: the CTA meets at the barriers
         const int64_t i = base + threadIdx.x;
         bool live = false, settled = true;
         PWords st;
@@ -327,7 +333,7 @@ __global__ void __launch_bounds__(256, MINB) k_pbfs_probe3(const Pb3Params p) {
         __syncthreads();
         if (threadIdx.x == 0) {
             int total = 0;
-            for (int w = 0; w < 8; ++w) {
+            for (int w = 0; w < NT / 32; ++w) {
                 const int c = s_wneed[w];
                 s_wneed[w] = total;
                 total += c;
@@ -445,8 +451,16 @@ __global__ void __launch_bounds__(256) k_pbfs_commit3(const Pb3Params p) {
     const unsigned long long o = p.gid[place];
     if (o == ~0ull) return;  // a hole: reserved, never claimed
     const int64_t ord = (int64_t)(o & ~PB_IN_ROUND);
-    const int64_t par = ord / 12;
-    const int act = (int)(ord % 12);
+    int64_t par;
+    int act;
+    if (((uint64_t)ord >> 32) == 0ull) {
+        const uint32_t o32 = (uint32_t)ord, p32 = o32 / 12u;
+        par = p32;
+        act = (int)(o32 - 12u * p32);
+    } else {
+        par = ord / 12;
+        act = (int)(ord % 12);
+    }
     const unsigned m16 = (p.mask32[par >> 1] >> (16 * (int)(par & 1))) & 0xFFFFu;
     p.gid[place] = (unsigned long long)(p.ctl[CTL_GID_BASE] + p.excl[par] + __popc(m16 & ((1u << act) - 1u)));
     p.parent[place] = p.parent_base + par;
@@ -473,21 +487,26 @@ extern "C" int acx_pbfs_expand2(const uint64_t* nodes, const uint8_t* action, co
     }
     if ((uintptr_t)nodes & 31u) return acx_fail(ACX_ERR_ARG, "acx_pbfs_expand2: nodes must be 32-byte aligned");
     const size_t smem = (size_t)EX_SLOTS * 32 + (8 * PB_MAX_WORLD + 2 * PB_MAX_WORLD) * sizeof(unsigned) + PB_MAX_WORLD * sizeof(unsigned long long);
+    static const int want = [] {  // ACX_EXPAND_OCC=3|4 resident CTAs per SM (80 / 64 registers): tuning knob
+        const char* e = getenv("ACX_EXPAND_OCC");
+        return e ? atoi(e) : 4;
+    }();
+    auto kern = want >= 4 ? k_pbfs_expand2<4> : k_pbfs_expand2<3>;
     static int ctas_per_sm[ACX_MAX_DEVICES] = {0};
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= ACX_MAX_DEVICES) dev = 0;
     if (ctas_per_sm[dev] == 0) {
-        ACX_CUDA(cudaFuncSetAttribute(k_pbfs_expand2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ACX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int occ = 0;
-        ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_pbfs_expand2, EX_THREADS, smem));
+        ACX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, EX_THREADS, smem));
         ctas_per_sm[dev] = occ > 0 ? occ : 1;
     }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int64_t grid = (f + EX_THREADS - 1) / EX_THREADS;
     if (grid > (int64_t)sms * ctas_per_sm[dev]) grid = (int64_t)sms * ctas_per_sm[dev];
-    k_pbfs_expand2<<<(unsigned)grid, EX_THREADS, smem, (cudaStream_t)stream>>>(nodes, action, loc, gids, ord_base, f, m, cyclical, world,
-                                                                              region_cap, reinterpret_cast<unsigned long long*>(cursor), dst, ctl);
+    kern<<<(unsigned)grid, EX_THREADS, smem, (cudaStream_t)stream>>>(nodes, action, loc, gids, ord_base, f, m, cyclical, world, region_cap,
+                                                                    reinterpret_cast<unsigned long long*>(cursor), dst, ctl);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }
@@ -505,7 +524,7 @@ extern "C" int acx_pbfs_probe3(const uint64_t* recs, const int64_t* region_count
     p.table = table; p.tcap = tcap; p.nodes = nodes; p.node_cap = node_cap; p.gid = reinterpret_cast<unsigned long long*>(gid);
     p.n_local = reinterpret_cast<unsigned long long*>(n_local); p.round_start = round_start_dev;
     p.mins = reinterpret_cast<unsigned long long*>(mins); p.mask32 = mask32; p.ctl = ctl;
-    static const int occ = [] {  // ACX_PROBE_OCC=2..8 resident CTAs per SM: tuning knob
+    static const int occ = [] {  // ACX_PROBE_OCC=2..8 resident CTAs of 256 threads per SM: tuning knob
         const char* e = getenv("ACX_PROBE_OCC");
         return e ? atoi(e) : 8;
     }();
@@ -517,10 +536,10 @@ extern "C" int acx_pbfs_probe3(const uint64_t* recs, const int64_t* region_count
     int64_t gx = ((int64_t)sms * per_sm + n_regions - 1) / n_regions;
     if (gx > (region_cap + 255) / 256) gx = (region_cap + 255) / 256;
     const dim3 grid((unsigned)gx, (unsigned)n_regions);
-    if (per_sm == 8) k_pbfs_probe3<8><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
-    else if (per_sm == 6) k_pbfs_probe3<6><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
-    else if (per_sm == 4) k_pbfs_probe3<4><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
-    else k_pbfs_probe3<2><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    if (per_sm == 8) k_pbfs_probe3<256, 8><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else if (per_sm == 6) k_pbfs_probe3<256, 6><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else if (per_sm == 4) k_pbfs_probe3<256, 4><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else k_pbfs_probe3<256, 2><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }

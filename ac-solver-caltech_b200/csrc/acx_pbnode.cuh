@@ -81,6 +81,9 @@ __device__ __forceinline__ bool pb_equal(const PWords& a, const PWords& b) {
     return ((a.w[0] ^ b.w[0]) | (a.w[1] ^ b.w[1]) | (a.w[2] ^ b.w[2]) | (a.w[3] ^ b.w[3])) == 0ull;
 }
 
-__device__ __forceinline__ int pb_owner(uint64_t h, int world) { return (int)(((h >> 20) & 0x7FFFFFFFull) % (uint64_t)world); }
+// 31 bits of the hash modulo the world size, as a 32-bit remainder (a 64-bit one is a subroutine call per candidate)
+__device__ __forceinline__ int pb_owner(uint64_t h, int world) {
+    return world == 1 ? 0 : (int)((uint32_t)((h >> 20) & 0x7FFFFFFFull) % (uint32_t)world);
+}
 
 }  // namespace acx

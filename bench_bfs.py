@@ -71,7 +71,11 @@ def _timed_run(root, budget, cyclical, world, dev, chunk, prof=False):
         ph = torch.tensor([eng.timers[k] for k in keys], device=dev, dtype=torch.float64)
         dist.all_reduce(ph, op=dist.ReduceOp.MAX)
         phases = {k: round(1e3 * float(v), 3) for k, v in zip(keys, ph)}
-    out = {"solved": ok, "path": path, "n_seen": eng.n_nodes, "nodes_expanded": eng.n_expanded, "wall_s": float(dt[0]),
+    holes = torch.zeros(1, dtype=torch.int64, device=dev)
+    if prof and hasattr(shard, "n_local_dev"):  # places of the node store that were reserved and never claimed (acx_pbfs_probe3)
+        holes += (shard.gid[: int(shard.n_local_dev.item())] == -1).sum()
+    dist.all_reduce(holes)
+    out = {"solved": ok, "path": path, "n_seen": eng.n_nodes, "nodes_expanded": eng.n_expanded, "wall_s": float(dt[0]), "store_holes": int(holes[0]),
            "levels": list(eng.levels), "rounds": eng.rounds, "sent_bytes": int(sent[0]), "candidates": int(sent[1]),
            "transport": shard.transport, "nodes": type(shard).__name__, "engine": type(eng).__name__, "phase_ms": phases}
     shard.close()
@@ -138,7 +142,7 @@ def bfs_leg(dev, budget=10 ** 9, chunk_per_rank=1 << 20, large=True, peak_gbs=65
         "chunk_parents_per_round": chunk, "transport": best["transport"], "nodes": best["nodes"], "engine": best["engine"],
         "candidates": best["candidates"], "all_to_all_bytes_total": best["sent_bytes"],
         "nvlink_egress_gbs_per_rank": best["sent_bytes"] / world / dt / 1e9,
-        "phase_ms": prof["phase_ms"], "phase_ms_note": "max over ranks, from a separate run with a device sync per phase (%.1f ms in all)" % (1e3 * prof["wall_s"]),
+        "store_holes": prof["store_holes"], "phase_ms": prof["phase_ms"], "phase_ms_note": "max over ranks, from a separate run with a device sync per phase (%.1f ms in all)" % (1e3 * prof["wall_s"]),
         "roofline": {"bound": "hbm", "achieved": alg / dt / 1e9 / world, "peak": peak_gbs, "unit": "GB/s per GPU",
                      "frac": alg / dt / 1e9 / world / peak_gbs, "alg_bytes_per_node_expanded": alg / max(exp, 1),
                      "nvlink_frac": best["sent_bytes"] / world / dt / 1e9 / 900.0},
@@ -172,7 +176,7 @@ def main():
     sharded = len(sys.argv) > 1 and sys.argv[1] == "sharded"
     args = sys.argv[2:] if sharded else sys.argv[1:]
     budget = int(float(args[0])) if args else 10 ** 9
-    chunk = int(float(args[1])) if len(args) > 1 else 1 << 20
+    chunk = int(float(args[1])) if len(args) > 1 else int(os.environ.get("ACX_BFS_CHUNK", 1 << 20))
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)

@@ -8,7 +8,7 @@ run() {
 import json,sys
 for l in sys.stdin:
     if l.startswith('{'):
-        d=json.loads(l); print(json.dumps({k:d[k] for k in ('nodes_expanded_per_s','wall_s','parity','phase_ms','rounds')}))
+        d=json.loads(l); print(json.dumps({k:d[k] for k in ('nodes_expanded_per_s','wall_s','parity','phase_ms','rounds','store_holes')}))
 " || tail -5 gpurun_out/bfs_sweep.err
 }
 if [ $# -eq 0 ]; then set -- "ACX_PROBE_OCC=6" "ACX_PROBE_OCC=4" "ACX_PROBE_OCC=8" "ACX_PROBE_OCC=6 ACX_BFS_OVERLAP=0"; fi

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Per-source-line instruction counts of one kernel from an ncu report (needs -lineinfo + --import-source on):
 
-    python tools/ncu_hotlines.py gpurun_out/prof.ncu-rep [units] [top]
+    python tools/ncu_hotlines.py gpurun_out/prof.ncu-rep [units] [top] [kernel regex]
 
 prints warp instructions and stall samples per source line, divided by `units` (e.g. 32768 row-warps)."""
 import csv
@@ -12,7 +12,8 @@ import collections
 rep = sys.argv[1]
 units = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 14
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+kern = ["--kernel-name", "regex:" + sys.argv[4]] if len(sys.argv) > 4 else []
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"] + kern, capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 files = collections.OrderedDict()
 cur = None

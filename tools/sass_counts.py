@@ -15,7 +15,7 @@ PATTERNS = [("UBLKCP", r"\bUBLKCP"), ("SYNCS", r"\bSYNCS"), ("UTMACMDFLUSH", r"\
             ("STG.256", r"\bSTG\.E\.[A-Z0-9.]*256"), ("LDG.128", r"\bLDG\.E\.[A-Z0-9.]*128"), ("STG.128", r"\bSTG\.E\.[A-Z0-9.]*128"),
             ("ATOMG", r"\bATOMG"), ("REDG", r"\bREDG"), ("ATOMS", r"\bATOMS"), ("VOTE", r"\bVOTE"), ("PRMT", r"\bPRMT"),
             ("LDS", r"\bLDS"), ("STS", r"\bSTS"), ("BAR", r"\bBAR\."), ("MEMBAR", r"\bMEMBAR"), ("ACQBULK/DEPBAR", r"\bDEPBAR|\bACQBULK")]
-WANT = sys.argv[1:] or ["k_env_tiles", "k_rows_tma", "k_rows_simple", "k_expand_warp", "k_pbfs_expand2", "k_pbfs_probe2", "k_pbfs_commit2",
+WANT = sys.argv[1:] or ["k_env_tiles", "k_rows_tma", "k_rows_simple", "k_expand_warp", "k_pbfs_expand2", "k_pbfs_probe3", "k_pbfs_commit3",
                         "k_pbfs_decide", "k_pbfs_expand<", "k_search", "k_path_replay", "k_graph_blocks"]
 
 
