@@ -7,9 +7,11 @@ What changed is who drives a round.  ShardedBFS reads the record counts and the 
 twice per round; here the host enqueues every round of a level back to back:
 
     expand2 (records sorted by owner, whole 128-byte lines to the peers)  ->  all-gather of the G x G counts (also the
-    barrier behind which the peer stores are complete)  ->  probe2 (winner resolution fused in)  ->  all-reduce of
-    16 bits per parent (SUM == OR, as an int32 view)  +  all-reduce MIN of the two event orders  ->  decide (scan + the
-    reference's success / budget decision, into a control block on the device)  ->  commit2
+    barrier behind which the peer stores are complete)  ->  probe3 (a claim is final: the candidate reserves its place in
+    the node store, claims the slot with it and writes its state there; first discovery settled beside the node)  ->
+    all-reduce of 16 bits per parent (SUM == OR, as an int32 view)  +  all-reduce MIN of the two event orders  ->  decide
+    (scan + the reference's success / budget decision, into a control block on the device)  ->  commit3 (global id, parent
+    and action of the round's nodes: a streaming pass, the table is not touched again)
 
 and looks at the control block once per level.  After a stop code every later kernel returns at once.
 """
@@ -27,8 +29,9 @@ STOP_SOLVED, STOP_ERROR, STOP_BUDGET = 1, 2, 3
 
 
 class PlaneShard2(PlaneShard):
-    """PlaneShard whose regions hold runs padded to whole 128-byte lines (four records).  Three exchange buffers: the
-    records of round k are read by probe k, commit k and -- as the previous round -- probe k+1, while round k+2 lands."""
+    """PlaneShard whose regions hold runs padded to whole 128-byte lines (four records), with a node store that
+    acx_pbfs_probe3 appends to (head room for the rounds around a stop and for holes).  Three exchange buffers: the
+    records of round k are read by probe k while round k+1 lands and round k+2 may already be staged."""
 
     n_bufs = 3
 
@@ -72,9 +75,10 @@ class PlaneBFS(ShardedBFS):
         probe   probe of round k+1                      (follows probe k; needs the records of k+1 and the ring slot of k-1)
         commit  mask all-reduce, scan, decision, commit of round k
     The dependencies that remain: the all-gather of round k waits for this rank's probe of round k-1 and commit of round
-    k-2, so its completion means that every rank is there: the receive buffer that round k+1 lands in (one of three,
-    last read by probe k-1 as "previous round" and by commit k-2) is free everywhere; a provisional table entry met by probe k+1 belongs to round k+1 or to round k, whose records
-    are still in their receive buffer (acx_pbfs_probe2); decisions and commits stay in round order on one stream."""
+    k-2, so its completion means that every rank is there and the receive buffer that round k+1 lands in (one of three)
+    is free everywhere.  A probe needs nothing from the previous round's commit: a table slot names a place in the node
+    store that was written by the probe which claimed it, and a place below the round's start is a visited state whether
+    or not its global id has been written yet; decisions and commits stay in round order on one stream."""
 
     def __init__(self, root, budget, shard, chunk=1 << 20, group=None, overlap=True):
         super().__init__(root, budget, shard, chunk=chunk, group=group)

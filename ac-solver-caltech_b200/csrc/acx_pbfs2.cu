@@ -31,6 +31,7 @@
 #include "../../include/acx.h"
 #include "acx_common.h"
 #include "acx_pbnode.cuh"
+#include "acx_tma.cuh"
 
 #include <cub/device/device_scan.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
@@ -54,7 +55,7 @@ static constexpr int EX_SLOTS = EX_THREADS * EX_GM + 4 * PB_MAX_WORLD;  // stage
 // inverse of move a (ac_moves.py:188-206): 0<->2, 1<->3 (r_i r_j^{+-1}); 4<->8, 5<->9, 6<->10, 7<->11 (g <-> g^-1)
 __device__ __forceinline__ int pb_inverse_move(int a) { return a < 4 ? (a ^ 2) : (a < 8 ? a + 4 : a - 4); }
 
-template <int MINB>
+template <int MINB, bool BULK>
 __global__ void __launch_bounds__(EX_THREADS, MINB) k_pbfs_expand2(const uint64_t* __restrict__ nodes, const uint8_t* __restrict__ action,
                                                             const int64_t* __restrict__ loc, const int64_t* __restrict__ gids,
                                                             int64_t ord_base, int64_t f, int m, int cyclical, int world,
@@ -143,6 +144,7 @@ __global__ void __launch_bounds__(EX_THREADS, MINB) k_pbfs_expand2(const uint64_
             if (lane < world) s_wcnt[warp * PB_MAX_WORLD + lane] = mycnt;
             __syncthreads();
             if (tid < world) {  // thread o: prefix over the warps, padded run, one reservation in owner o's region
+                if (BULK) bulk_wait_read<0>();  // the bulk store this thread issued for the previous group has read the stage
                 unsigned tot = 0;
                 for (int w = 0; w < EX_THREADS / 32; ++w) {
                     const unsigned c = s_wcnt[w * PB_MAX_WORLD + tid];
@@ -176,22 +178,39 @@ __global__ void __launch_bounds__(EX_THREADS, MINB) k_pbfs_expand2(const uint64_
                     stage[2 * (s_off[tid] + q) + 1] = make_uint4(0u, 0u, 0u, 0u);
                 }
             }
-            __syncthreads();
-            for (int o = 0; o < world; ++o) {  // the run of owner o: consecutive threads, consecutive 16-byte pieces
-                const unsigned pad = s_pad[o] & 0xFFFFu;
-                if (pad == 0) continue;
-                const unsigned long long base = s_base[o];
-                if (base + pad > (unsigned long long)region_cap) {
-                    if (tid == 0) cursor[world] = 1ull;  // a region overflowed: the host raises
-                    continue;
+            if (BULK) {
+                // the run of owner o leaves as ONE bulk async copy (shared -> global, local or peer memory over NVLink),
+                // issued by thread o: no thread waits for the stores, the next four moves are computed meanwhile
+                fence_proxy_async();
+                __syncthreads();
+                if (tid < world) {
+                    const unsigned pad = s_pad[tid] & 0xFFFFu;
+                    const unsigned long long base = s_base[tid];
+                    if (pad != 0) {
+                        if (base + pad > (unsigned long long)region_cap) cursor[world] = 1ull;  // a region overflowed: the host raises
+                        else bulk_store(dst.region[tid] + base * 32ull, smem_u32(stage + 2 * s_off[tid]), pad * 32u);
+                    }
+                    bulk_commit();
                 }
-                uint4* out = reinterpret_cast<uint4*>(dst.region[o] + base * 32ull);
-                const uint4* in = stage + 2 * s_off[o];
-                for (unsigned q = tid; q < 2 * pad; q += EX_THREADS) out[q] = in[q];
+            } else {
+                __syncthreads();
+                for (int o = 0; o < world; ++o) {  // the run of owner o: consecutive threads, consecutive 16-byte pieces
+                    const unsigned pad = s_pad[o] & 0xFFFFu;
+                    if (pad == 0) continue;
+                    const unsigned long long base = s_base[o];
+                    if (base + pad > (unsigned long long)region_cap) {
+                        if (tid == 0) cursor[world] = 1ull;  // a region overflowed: the host raises
+                        continue;
+                    }
+                    uint4* out = reinterpret_cast<uint4*>(dst.region[o] + base * 32ull);
+                    const uint4* in = stage + 2 * s_off[o];
+                    for (unsigned q = tid; q < 2 * pad; q += EX_THREADS) out[q] = in[q];
+                }
             }
             __syncthreads();
         }
     }
+    if (BULK && tid < world) bulk_wait_all<0>();  // the stage must outlive the copies that read it
 }
 
 struct Pb3Params {
@@ -491,7 +510,11 @@ extern "C" int acx_pbfs_expand2(const uint64_t* nodes, const uint8_t* action, co
         const char* e = getenv("ACX_EXPAND_OCC");
         return e ? atoi(e) : 4;
     }();
-    auto kern = want >= 4 ? k_pbfs_expand2<4> : k_pbfs_expand2<3>;
+    static const bool bulk = [] {  // ACX_EXPAND_BULK=0: per-thread 16-byte stores instead of one bulk async copy per run
+        const char* e = getenv("ACX_EXPAND_BULK");
+        return !(e && atoi(e) == 0);
+    }();
+    auto kern = bulk ? (want >= 4 ? k_pbfs_expand2<4, true> : k_pbfs_expand2<3, true>) : (want >= 4 ? k_pbfs_expand2<4, false> : k_pbfs_expand2<3, false>);
     static int ctas_per_sm[ACX_MAX_DEVICES] = {0};
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
