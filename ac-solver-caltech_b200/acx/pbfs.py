@@ -134,16 +134,15 @@ class PlaneBFS(ShardedBFS):
             return cur
 
         def gather(k, cur):
-            """stage stream: the count all-gather of round k, once this rank has committed round k-2 and probed round k-1 --
-            when it completes, every rank has written its records of round k and is done with the buffer (one of three)
-            that round k+1 will land in"""
+            """stage stream: the count all-gather of round k, once this rank has committed round k-2 -- when it completes,
+            every rank has written its records of round k and is done with the receive buffer (one of three, read by the
+            probe of its round only) that round k+1 will land in.  It does not wait for the probe of round k-1: the
+            latency of the collective is hidden behind that probe."""
             allc = allcs[k % 3]
             with torch.cuda.stream(st_stage):
                 if pipe:
                     if (k - 2) in commit_ev:
                         st_stage.wait_event(commit_ev[k - 2])
-                    if (k - 1) in probed_ev:
-                        st_stage.wait_event(probed_ev[k - 1])
                 if G > 1:
                     dist.all_gather_into_tensor(allc, cur, group=self.group)
                 ev = torch.cuda.Event()
