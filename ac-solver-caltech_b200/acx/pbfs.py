@@ -16,6 +16,7 @@ twice per round; here the host enqueues every round of a level back to back:
 and looks at the control block once per level.  After a stop code every later kernel returns at once.
 """
 import ctypes
+import os
 
 import torch
 import torch.distributed as dist
@@ -26,6 +27,21 @@ from .bfs_sharded import PlaneShard, ShardedBFS
 
 SENT = 1 << 62
 STOP_SOLVED, STOP_ERROR, STOP_BUDGET = 1, 2, 3
+
+
+_count_groups = {}
+
+
+def _count_group(group):
+    """A second communicator over the same ranks for the count all-gathers.  NCCL runs the collectives of ONE communicator
+    in issue order, so on the search's own communicator the all-gather of round k+1 would queue behind the mask all-reduce
+    of round k -- which waits for probe k -- and its latency would be exposed in every round; on a communicator of its own
+    it completes while probe k runs.  Collective call: every rank creates it at the same point (PlaneBFS.__init__)."""
+    key = id(group) if group is not None else 0
+    if key not in _count_groups:
+        ranks = dist.get_process_group_ranks(group if group is not None else dist.group.WORLD)
+        _count_groups[key] = dist.new_group(ranks=ranks, backend="nccl")
+    return _count_groups[key]
 
 
 class PlaneShard2(PlaneShard):
@@ -87,8 +103,25 @@ class PlaneBFS(ShardedBFS):
         if self.chunk > (1 << 31) // 12 - 1:
             raise ValueError("chunk: the new nodes of a round are counted in 32 bits")
         self.overlap = bool(overlap)
+        self.count_group = _count_group(group) if (self.world > 1 and self.overlap) else group
+
+    def _dump_trace(self, trace, path):
+        import json
+
+        torch.cuda.synchronize(self.dev)
+        t0 = trace[0][2]
+        rows = [(name, k, round(1e3 * t0.elapsed_time(ev), 1)) for name, k, ev in trace[1:]]  # microseconds since the start
+        with open("%s_rank%d.json" % (path, self.rank), "w") as f:
+            json.dump(rows, f)
 
     def run(self):
+        try:
+            return self._run()
+        finally:
+            if getattr(self, "_trace", None):
+                self._dump_trace(*self._trace)
+
+    def _run(self):
         s, G, dev, L = self.shard, self.world, self.dev, self.shard.L
         rank, C_max = self.rank, self.chunk
         if s.owner_of_row(self.root, G) == rank:
@@ -122,29 +155,49 @@ class PlaneBFS(ShardedBFS):
         commit_ev, probed_ev = {}, {}  # round -> event behind its commit / its probe (the last few are kept)
         lo, hi, first = 0, 1, 0
         n_local = s.n_local()
+        # ACX_BFS_TRACE=<path prefix>: a device-side time line of the pipeline (one event per step and stream), for tuning
+        trace_to = os.environ.get("ACX_BFS_TRACE") if pipe else None
+        trace = []
+
+        def mk(stream, name, k):
+            if trace_to:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record(stream)
+                trace.append((name, k, ev))
+
+        mk(main, "t0", -1)
+        self._trace = (trace, trace_to) if trace_to else None
 
         def stage(k, off, a, b):
             """stage stream: expand the local parents of round k and route the records to their owners"""
             cur = cursors[k % 3]
             with torch.cuda.stream(st_stage):
+                if pipe and (k - 3) in commit_ev:
+                    st_stage.wait_event(commit_ev[k - 3])  # on one rank the decision of round k-3 read these counts
                 cur.zero_()
+                mk(st_stage, "expand_begin", k)
                 if b > a:
                     _lib.check(L.acx_pbfs_expand2(_ptr(s.nodes), _ptr(s.action), loc[a:b].data_ptr(), gids[a:b].data_ptr(), off, b - a,
                                                   s.m, int(s.cyc), G, s.rcap, _ptr(cur), dsts[k % 3], _ptr(ctl), st_stage.cuda_stream), "acx_pbfs_expand2")
+                mk(st_stage, "expand_end", k)
             return cur
 
         def gather(k, cur):
-            """stage stream: the count all-gather of round k, once this rank has committed round k-2 -- when it completes,
-            every rank has written its records of round k and is done with the receive buffer (one of three, read by the
-            probe of its round only) that round k+1 will land in.  It does not wait for the probe of round k-1: the
-            latency of the collective is hidden behind that probe."""
+            """stage stream: the count all-gather of round k, once this rank has probed round k-2 -- when it completes, every
+            rank has written its records of round k and is done with the receive buffer (one of three, read by the probe
+            of its round only) that round k+1 will land in.  It waits neither for the probe of round k-1 nor for the
+            commit of round k-2, and it runs on a communicator of its own (_count_group): its latency hides behind probe k-1."""
             allc = allcs[k % 3]
             with torch.cuda.stream(st_stage):
                 if pipe:
-                    if (k - 2) in commit_ev:
-                        st_stage.wait_event(commit_ev[k - 2])
+                    if (k - 2) in probed_ev:
+                        st_stage.wait_event(probed_ev[k - 2])
+                    if (k - 3) in commit_ev:
+                        st_stage.wait_event(commit_ev[k - 3])  # the decision of round k-3 read this ring slot of the counts
+                mk(st_stage, "allgather_begin", k)
                 if G > 1:
-                    dist.all_gather_into_tensor(allc, cur, group=self.group)
+                    dist.all_gather_into_tensor(allc, cur, group=self.count_group)
+                mk(st_stage, "allgather_end", k)
                 ev = torch.cuda.Event()
                 ev.record(st_stage)
             return (allc if G > 1 else cur), ev
@@ -190,25 +243,29 @@ class PlaneBFS(ShardedBFS):
                 mask16[r2][: (C + 1) // 2 * 2].zero_()
                 mins[r2].fill_(SENT)
                 starts[r2].copy_(s.n_local_dev)
+                mk(main, "probe_begin", k)
                 _lib.check(L.acx_pbfs_probe3(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(s.table), s.tcap, _ptr(s.nodes), s.cap, _ptr(s.gid),
                                              _ptr(s.n_local_dev), _ptr(starts[r2]), _ptr(mins[r2]), _ptr(mask32[r2]), _ptr(ctl),
                                              main.cuda_stream), "acx_pbfs_probe3")
                 ends[r2].copy_(s.n_local_dev)
+                mk(main, "probe_end", k)
                 self._tick("probe")
                 probed = torch.cuda.Event()
                 probed.record(main)
                 probed_ev[k] = probed
-                probed_ev.pop(k - 3, None)
+                probed_ev.pop(k - 4, None)
                 # ---- commit stream
                 with torch.cuda.stream(st_commit):
                     if pipe:
                         st_commit.wait_event(probed)
+                    mk(st_commit, "reduce_begin", k)
                     if G > 1:
                         if self.timers is not None:
                             dist.barrier(group=self.group)
                             self._tick("wait_slowest_rank")
                         dist.all_reduce(mask32[r2][: (C + 1) // 2], group=self.group)
                         dist.all_reduce(mins[r2], op=dist.ReduceOp.MIN, group=self.group)
+                    mk(st_commit, "reduce_end", k)
                     cs = st_commit.cuda_stream
                     rcd = int(L.acx_pbfs_decide(_ptr(mask16[r2]), _ptr(excl), C, _ptr(mins[r2]), off, self.budget, _ptr(ctl), _ptr(counts), G,
                                                 rank, _ptr(temp), need, cs))
@@ -218,9 +275,10 @@ class PlaneBFS(ShardedBFS):
                     _lib.check(L.acx_pbfs_commit3(_ptr(starts[r2]), _ptr(ends[r2]), G * s.rcap, s.cap, _ptr(excl), _ptr(mask32[r2]), off,
                                                   _ptr(ctl), _ptr(s.gid), _ptr(s.parent), _ptr(s.action), cs), "acx_pbfs_commit3")
                     self._tick("commit")
+                    mk(st_commit, "commit_end", k)
                     commit_ev[k] = torch.cuda.Event()
                     commit_ev[k].record(st_commit)
-                    commit_ev.pop(k - 3, None)
+                    commit_ev.pop(k - 5, None)
                     mirror[ring].copy_(ctl, non_blocking=True)
                     events[ring] = torch.cuda.Event()
                     events[ring].record(st_commit)
@@ -231,6 +289,7 @@ class PlaneBFS(ShardedBFS):
             if pipe:  # join: the level's commits, and a staged round that may still be in flight after an early exit
                 main.wait_stream(st_commit)
                 main.wait_stream(st_stage)
+            mk(main, "level_end", len(self.levels))
             c = torch.cat([ctl, s.n_local_dev]).tolist()  # the one read-back of the level
             n_local = c[16]
             self.n_nodes, self.n_expanded = c[1], c[2]

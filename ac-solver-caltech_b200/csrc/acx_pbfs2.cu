@@ -465,10 +465,11 @@ __global__ void k_pbfs_decide(const uint16_t* mask16, const int32_t* excl, int64
 // the nodes the probe appended in this round: order -> (global id, parent, action)
 __global__ void __launch_bounds__(256) k_pbfs_commit3(const Pb3Params p) {
     if (p.ctl[CTL_STOP] != 0) return;
-    const int64_t place = *p.round_start + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (place >= *p.round_end || place >= p.node_cap) return;
+    const int64_t re = *p.round_end < p.node_cap ? *p.round_end : p.node_cap;
+    const int64_t gid_base = p.ctl[CTL_GID_BASE];
+  for (int64_t place = *p.round_start + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; place < re; place += (int64_t)gridDim.x * blockDim.x) {
     const unsigned long long o = p.gid[place];
-    if (o == ~0ull) return;  // a hole: reserved, never claimed
+    if (o == ~0ull) continue;  // a hole: reserved, never claimed
     const int64_t ord = (int64_t)(o & ~PB_IN_ROUND);
     int64_t par;
     int act;
@@ -481,9 +482,10 @@ __global__ void __launch_bounds__(256) k_pbfs_commit3(const Pb3Params p) {
         act = (int)(ord % 12);
     }
     const unsigned m16 = (p.mask32[par >> 1] >> (16 * (int)(par & 1))) & 0xFFFFu;
-    p.gid[place] = (unsigned long long)(p.ctl[CTL_GID_BASE] + p.excl[par] + __popc(m16 & ((1u << act) - 1u)));
+    p.gid[place] = (unsigned long long)(gid_base + p.excl[par] + __popc(m16 & ((1u << act) - 1u)));
     p.parent[place] = p.parent_base + par;
     p.action[place] = (uint8_t)act;
+  }
 }
 
 }  // namespace acx
@@ -598,7 +600,12 @@ extern "C" int acx_pbfs_commit3(const int64_t* round_start_dev, const int64_t* r
     p.round_start = round_start_dev; p.round_end = round_end_dev; p.node_cap = node_cap;
     p.excl = excl; p.mask32 = const_cast<unsigned*>(mask32); p.parent_base = parent_base;
     p.ctl = const_cast<int64_t*>(ctl); p.gid = reinterpret_cast<unsigned long long*>(gid); p.parent = parent; p.action = action;
-    k_pbfs_commit3<<<(unsigned)((max_new + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int64_t grid = (max_new + 255) / 256;  // the round's size is known on the device only: a grid-stride loop over it
+    if (grid > (int64_t)sms * 8) grid = (int64_t)sms * 8;
+    k_pbfs_commit3<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(p);
     ACX_CUDA(cudaGetLastError());
     return ACX_OK;
 }
