@@ -44,7 +44,7 @@ _SIGNATURES = {
     "acx_pbfs_expand2": (_I32, [_PTR, _PTR, _PTR, _PTR, _I64, _I64, _I32, _I32, _I32, _I64, _PTR, _PTR, _PTR, _PTR]),
     "acx_pbfs_probe3": (_I32, [_PTR, _PTR, _I64, _I32, _I64, _PTR, _I64, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR]),
     "acx_pbfs_decide": (_I64, [_PTR, _PTR, _I64, _PTR, _I64, _I64, _PTR, _PTR, _I32, _I32, _PTR, _I64, _PTR]),
-    "acx_pbfs_commit3": (_I32, [_PTR, _PTR, _I64, _I64, _PTR, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR]),
+    "acx_pbfs_commit3": (_I32, [_PTR, _PTR, _I64, _I64, _PTR, _PTR, _I64, _PTR, _PTR, _PTR, _PTR, _PTR, _PTR]),
     "acx_bfs_mask_scan": (_I64, [_PTR, _I64, _PTR, _PTR, _PTR, _I64, _PTR]),
     "acx_bfs_mask_scan_static": (_I32, [_PTR, _I64, _PTR, _PTR, _PTR]),
     "acx_bfs_window_partition": (_I32, [_PTR, _I64, _I64, _I64, _I64, _PTR, _PTR, _PTR, _I64, _PTR, _PTR, _I32, _PTR]),

@@ -18,6 +18,7 @@ and looks at the control block once per level.  After a stop code every later ke
 import ctypes
 import os
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -150,6 +151,10 @@ class PlaneBFS(ShardedBFS):
         # the host runs at most `ahead` rounds in front of the device: it waits for the event of round k - ahead, looks
         # at that round's copy of the stop code (pinned memory) and stops enqueueing when the search has ended
         ahead = 4
+        WB = 64  # windows grouped per pass over the level's nodes
+        LOGCAP = 4096  # rounds of one level whose place ranges are logged (a longer level is grouped from all its nodes)
+        round_log = torch.zeros((LOGCAP, 4), dtype=torch.int64, device=dev)
+        prev_log, level_k0 = None, 0  # the log of the previous level (numpy [rounds, 4]), first round of this level
         mirror = torch.zeros((ahead + 1, 16), dtype=torch.int64).pin_memory()
         events = [None] * (ahead + 1)
         commit_ev, probed_ev = {}, {}  # round -> event behind its commit / its probe (the last few are kept)
@@ -207,91 +212,118 @@ class PlaneBFS(ShardedBFS):
             self._tick(None)
             gl = s.gid[first:n_local]
             nwin = (hi - lo + C_max - 1) // C_max
-            if nwin == 1:  # one round: the local frontier as it is (no grouping pass, no read-back)
-                loc, gids, cuts = torch.arange(first, n_local, dtype=torch.int64, device=dev), gl, [0, n_local - first]
-            else:
-                loc, gids, cuts = s.window_partition(gl, first, lo, C_max, nwin)
-            first = n_local
-            self._tick("level_sort")
-            offs = list(range(lo, hi, C_max))
-            if pipe:
-                st_stage.wait_stream(main)  # loc / gids of this level; every commit of the previous level (joined below)
-                st_commit.wait_stream(main)
-            cur = stage(self.rounds, offs[0], cuts[0], cuts[1])
-            self._tick("expand_exchange")
-            pending = gather(self.rounds, cur)
-            self._tick("count_allgather")
-            for i, off in enumerate(offs):
-                C = min(C_max, hi - off)
-                k = self.rounds
-                ring = k % (ahead + 1)
-                if events[ring] is not None:
-                    events[ring].synchronize()
-                    if int(mirror[ring, 0]) != 0:
-                        break
-                r2 = k % 2
-                buf = recv[k % 3]
-                counts, ready = pending
-                nxt = stage(k + 1, offs[i + 1], cuts[i + 1], cuts[i + 2]) if i + 1 < len(offs) else None
-                self._tick("expand_exchange")
-                rc_ptr = counts.data_ptr() + 8 * rank  # records rank s staged for this rank: counts[s * (G + 1) + rank]
-                # ---- probe stream (main)
+            stopped = False
+            # The level's windows (rounds) are grouped WB at a time: a level that the budget cuts after a few rounds -- the last
+            # one, the largest -- is not sorted beyond them, and the grouping buffers hold one block's nodes at a time.
+            for wb in range(0, nwin, WB):
+                nb = min(WB, nwin - wb)
+                blo = lo + wb * C_max
+                bhi = min(hi, blo + nb * C_max)
+                if wb and pipe:
+                    main.wait_stream(st_stage)  # the staged rounds of the previous block read the grouping buffers
+                if nwin == 1:  # one round: the local frontier as it is (no grouping pass, no read-back)
+                    loc = torch.arange(first, n_local, dtype=torch.int64, device=dev, out=s._part[0][: n_local - first])
+                    gids, cuts = gl, [0, n_local - first]
+                else:
+                    a, b = first, n_local
+                    if prev_log is not None:
+                        # the rounds of the previous level appended their nodes to contiguous places, with contiguous
+                        # global ids: only the places of the rounds that reach into this block of windows are grouped
+                        hit = (prev_log[:, 2] < bhi) & (prev_log[:, 2] + prev_log[:, 3] > blo) & (prev_log[:, 1] > prev_log[:, 0])
+                        if hit.any():
+                            a, b = max(first, int(prev_log[hit, 0].min())), min(n_local, int(prev_log[hit, 1].max()))
+                        else:
+                            a = b = first
+                    loc, gids, cuts = s.window_partition(s.gid[a:b], a, blo, C_max, nb)
+                self._tick("level_sort")
+                offs = list(range(blo, bhi, C_max))
                 if pipe:
-                    main.wait_event(ready)
-                    if (k - 2) in commit_ev:
-                        main.wait_event(commit_ev[k - 2])  # slot / mask / mins of this ring position are free again
-                mask16[r2][: (C + 1) // 2 * 2].zero_()
-                mins[r2].fill_(SENT)
-                starts[r2].copy_(s.n_local_dev)
-                mk(main, "probe_begin", k)
-                _lib.check(L.acx_pbfs_probe3(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(s.table), s.tcap, _ptr(s.nodes), s.cap, _ptr(s.gid),
-                                             _ptr(s.n_local_dev), _ptr(starts[r2]), _ptr(mins[r2]), _ptr(mask32[r2]), _ptr(ctl),
-                                             main.cuda_stream), "acx_pbfs_probe3")
-                ends[r2].copy_(s.n_local_dev)
-                mk(main, "probe_end", k)
-                self._tick("probe")
-                probed = torch.cuda.Event()
-                probed.record(main)
-                probed_ev[k] = probed
-                probed_ev.pop(k - 4, None)
-                # ---- commit stream
-                with torch.cuda.stream(st_commit):
+                    st_stage.wait_stream(main)  # loc / gids of this block; every commit of the previous level (joined below)
+                    st_commit.wait_stream(main)
+                cur = stage(self.rounds, offs[0], cuts[0], cuts[1])
+                self._tick("expand_exchange")
+                pending = gather(self.rounds, cur)
+                self._tick("count_allgather")
+                for i, off in enumerate(offs):
+                    C = min(C_max, hi - off)
+                    k = self.rounds
+                    ring = k % (ahead + 1)
+                    if events[ring] is not None:
+                        events[ring].synchronize()
+                        if int(mirror[ring, 0]) != 0:
+                            stopped = True
+                            break
+                    r2 = k % 2
+                    buf = recv[k % 3]
+                    counts, ready = pending
+                    nxt = stage(k + 1, offs[i + 1], cuts[i + 1], cuts[i + 2]) if i + 1 < len(offs) else None
+                    self._tick("expand_exchange")
+                    rc_ptr = counts.data_ptr() + 8 * rank  # records rank s staged for this rank: counts[s * (G + 1) + rank]
+                    # ---- probe stream (main)
                     if pipe:
-                        st_commit.wait_event(probed)
-                    mk(st_commit, "reduce_begin", k)
-                    if G > 1:
-                        if self.timers is not None:
-                            dist.barrier(group=self.group)
-                            self._tick("wait_slowest_rank")
-                        dist.all_reduce(mask32[r2][: (C + 1) // 2], group=self.group)
-                        dist.all_reduce(mins[r2], op=dist.ReduceOp.MIN, group=self.group)
-                    mk(st_commit, "reduce_end", k)
-                    cs = st_commit.cuda_stream
-                    rcd = int(L.acx_pbfs_decide(_ptr(mask16[r2]), _ptr(excl), C, _ptr(mins[r2]), off, self.budget, _ptr(ctl), _ptr(counts), G,
-                                                rank, _ptr(temp), need, cs))
-                    if rcd:
-                        _lib.check(rcd, "acx_pbfs_decide")
-                    self._tick("reduce_scan_decide")
-                    _lib.check(L.acx_pbfs_commit3(_ptr(starts[r2]), _ptr(ends[r2]), G * s.rcap, s.cap, _ptr(excl), _ptr(mask32[r2]), off,
-                                                  _ptr(ctl), _ptr(s.gid), _ptr(s.parent), _ptr(s.action), cs), "acx_pbfs_commit3")
-                    self._tick("commit")
-                    mk(st_commit, "commit_end", k)
-                    commit_ev[k] = torch.cuda.Event()
-                    commit_ev[k].record(st_commit)
-                    commit_ev.pop(k - 5, None)
-                    mirror[ring].copy_(ctl, non_blocking=True)
-                    events[ring] = torch.cuda.Event()
-                    events[ring].record(st_commit)
-                self.rounds += 1
-                if nxt is not None:
-                    pending = gather(k + 1, nxt)
-                    self._tick("count_allgather")
+                        main.wait_event(ready)
+                        if (k - 2) in commit_ev:
+                            main.wait_event(commit_ev[k - 2])  # slot / mask / mins of this ring position are free again
+                    mask16[r2][: (C + 1) // 2 * 2].zero_()
+                    mins[r2].fill_(SENT)
+                    starts[r2].copy_(s.n_local_dev)
+                    mk(main, "probe_begin", k)
+                    _lib.check(L.acx_pbfs_probe3(_ptr(buf), rc_ptr, G + 1, G, s.rcap, _ptr(s.table), s.tcap, _ptr(s.nodes), s.cap, _ptr(s.gid),
+                                                 _ptr(s.n_local_dev), _ptr(starts[r2]), _ptr(mins[r2]), _ptr(mask32[r2]), _ptr(ctl),
+                                                 main.cuda_stream), "acx_pbfs_probe3")
+                    ends[r2].copy_(s.n_local_dev)
+                    mk(main, "probe_end", k)
+                    self._tick("probe")
+                    probed = torch.cuda.Event()
+                    probed.record(main)
+                    probed_ev[k] = probed
+                    probed_ev.pop(k - 4, None)
+                    # ---- commit stream
+                    with torch.cuda.stream(st_commit):
+                        if pipe:
+                            st_commit.wait_event(probed)
+                        mk(st_commit, "reduce_begin", k)
+                        if G > 1:
+                            if self.timers is not None:
+                                dist.barrier(group=self.group)
+                                self._tick("wait_slowest_rank")
+                            dist.all_reduce(mask32[r2][: (C + 1) // 2], group=self.group)
+                            dist.all_reduce(mins[r2], op=dist.ReduceOp.MIN, group=self.group)
+                        mk(st_commit, "reduce_end", k)
+                        cs = st_commit.cuda_stream
+                        rcd = int(L.acx_pbfs_decide(_ptr(mask16[r2]), _ptr(excl), C, _ptr(mins[r2]), off, self.budget, _ptr(ctl), _ptr(counts), G,
+                                                    rank, _ptr(temp), need, cs))
+                        if rcd:
+                            _lib.check(rcd, "acx_pbfs_decide")
+                        self._tick("reduce_scan_decide")
+                        _lib.check(L.acx_pbfs_commit3(_ptr(starts[r2]), _ptr(ends[r2]), G * s.rcap, s.cap, _ptr(excl), _ptr(mask32[r2]), off,
+                                                      _ptr(ctl), _ptr(s.gid), _ptr(s.parent), _ptr(s.action),
+                                                  round_log[k - level_k0].data_ptr() if k - level_k0 < LOGCAP else 0, cs), "acx_pbfs_commit3")
+                        self._tick("commit")
+                        mk(st_commit, "commit_end", k)
+                        commit_ev[k] = torch.cuda.Event()
+                        commit_ev[k].record(st_commit)
+                        commit_ev.pop(k - 5, None)
+                        mirror[ring].copy_(ctl, non_blocking=True)
+                        events[ring] = torch.cuda.Event()
+                        events[ring].record(st_commit)
+                    self.rounds += 1
+                    if nxt is not None:
+                        pending = gather(k + 1, nxt)
+                        self._tick("count_allgather")
+                if stopped:
+                    break
+            first = n_local
             if pipe:  # join: the level's commits, and a staged round that may still be in flight after an early exit
                 main.wait_stream(st_commit)
                 main.wait_stream(st_stage)
             mk(main, "level_end", len(self.levels))
-            c = torch.cat([ctl, s.n_local_dev]).tolist()  # the one read-back of the level
+            n_logged = self.rounds - level_k0
+            logged = n_logged <= LOGCAP
+            c = torch.cat([ctl, s.n_local_dev, round_log[:n_logged].flatten() if logged else round_log[:0].flatten()]).tolist()  # the one read-back of the level
             n_local = c[16]
+            prev_log = np.asarray(c[17:], dtype=np.int64).reshape(-1, 4) if logged else None
+            level_k0 = self.rounds
             self.n_nodes, self.n_expanded = c[1], c[2]
             if c[6]:
                 raise RuntimeError("plane bfs: a send region or the node store overflowed (hash imbalance above the head room)")

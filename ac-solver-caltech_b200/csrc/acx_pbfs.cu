@@ -530,15 +530,15 @@ namespace acx {
 static constexpr int WIN_ITEMS = 16, WIN_BINS = 1024;
 
 template <bool SCATTER>
-__global__ void __launch_bounds__(256) k_win_part(const int64_t* gid, int64_t n, int64_t lo, int64_t chunk, unsigned long long* counts,
+__global__ void __launch_bounds__(256) k_win_part(const int64_t* gid, int64_t n, int64_t lo, int64_t chunk, int64_t n_windows, unsigned long long* counts,
                                                   const int64_t* offsets, unsigned long long* cursor, int64_t first,
                                                   int64_t* loc_out, int64_t* gid_out) {
     __shared__ unsigned s_cnt[WIN_BINS];
     __shared__ unsigned long long s_base[WIN_BINS];
     __shared__ int s_wmin, s_wmax;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int shift = (chunk & (chunk - 1)) == 0 ? 63 - __clzll(chunk) : -1;
     const int64_t i0 = (int64_t)blockIdx.x * (WIN_ITEMS * 256) + tid;
-    for (int t = tid; t < WIN_BINS; t += 256) s_cnt[t] = 0u;
     if (tid == 0) {
         s_wmin = 0x7FFFFFFF;
         s_wmax = -1;
@@ -554,18 +554,27 @@ __global__ void __launch_bounds__(256) k_win_part(const int64_t* gid, int64_t n,
         g[k] = 0;
         if (i < n) {
             g[k] = gid[i];
-            if (g[k] >= lo) {  // gid -1: a hole of the node store (acx_pbfs_probe3), not a node
-                w[k] = (int)((g[k] - lo) / chunk);
-                mn = min(mn, w[k]);
-                mx = max(mx, w[k]);
+            // outside [lo, lo + n_windows * chunk): another block of the level's windows, or gid -1 = a hole of the node
+            // store (acx_pbfs_probe3), not a node
+            if (g[k] >= lo) {
+                // a 64-bit division per node costs more than the pass over the ids: chunks are powers of two in practice
+                const int64_t wk = shift >= 0 ? ((g[k] - lo) >> shift) : (g[k] - lo) / chunk;
+                if (wk < n_windows) {
+                    w[k] = (int)wk;
+                    mn = min(mn, w[k]);
+                    mx = max(mx, w[k]);
+                }
             }
         }
     }
-    if (mx >= 0) {
+    mn = __reduce_min_sync(0xFFFFFFFFu, mn);  // one shared-memory atomic per warp, not per thread
+    mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+    if (lane == 0 && mx >= 0) {
         atomicMin(&s_wmin, mn);
         atomicMax(&s_wmax, mx);
     }
     __syncthreads();
+    if (s_wmax < 0) return;  // nothing of this block of windows in these nodes
     const int wmin = s_wmin, range = s_wmax - s_wmin + 1;
     if (range > WIN_BINS) {  // rare: straight global atomics
 #pragma unroll
@@ -581,9 +590,20 @@ __global__ void __launch_bounds__(256) k_win_part(const int64_t* gid, int64_t n,
         }
         return;
     }
+    for (int t = tid; t < range; t += 256) s_cnt[t] = 0u;
+    __syncthreads();
     unsigned rank[WIN_ITEMS];
 #pragma unroll
-    for (int k = 0; k < WIN_ITEMS; ++k) rank[k] = w[k] >= 0 ? atomicAdd(&s_cnt[w[k] - wmin], 1u) : 0u;
+    for (int k = 0; k < WIN_ITEMS; ++k) {
+        // consecutive nodes mostly share a window: the lanes of a warp with the same window take their ranks with ONE
+        // shared-memory atomic (32 same-address atomics of a warp serialize)
+        const unsigned grp = __match_any_sync(0xFFFFFFFFu, w[k]);
+        const int leader = __ffs(grp) - 1;
+        unsigned base = 0u;
+        if (lane == leader && w[k] >= 0) base = atomicAdd(&s_cnt[w[k] - wmin], (unsigned)__popc(grp));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        rank[k] = base + __popc(grp & ((1u << lane) - 1u));
+    }
     __syncthreads();
     for (int t = tid; t < range; t += 256) {
         if (!s_cnt[t]) continue;
@@ -610,11 +630,11 @@ extern "C" int acx_bfs_window_partition(const int64_t* gid, int64_t n, int64_t l
     const unsigned grid = (unsigned)((n + WIN_ITEMS * 256 - 1) / (WIN_ITEMS * 256));
     if (phase == 0) {
         if (!gid || !counts) return acx_fail(ACX_ERR_ARG, "acx_bfs_window_partition: null pointer");
-        k_win_part<false><<<grid, 256, 0, (cudaStream_t)stream>>>(gid, n, lo, chunk, reinterpret_cast<unsigned long long*>(counts), nullptr,
+        k_win_part<false><<<grid, 256, 0, (cudaStream_t)stream>>>(gid, n, lo, chunk, n_windows, reinterpret_cast<unsigned long long*>(counts), nullptr,
                                                                  nullptr, first, nullptr, nullptr);
     } else {
         if (!gid || !offsets || !cursor || !loc_out || !gid_out) return acx_fail(ACX_ERR_ARG, "acx_bfs_window_partition: null pointer");
-        k_win_part<true><<<grid, 256, 0, (cudaStream_t)stream>>>(gid, n, lo, chunk, nullptr, offsets,
+        k_win_part<true><<<grid, 256, 0, (cudaStream_t)stream>>>(gid, n, lo, chunk, n_windows, nullptr, offsets,
                                                                 reinterpret_cast<unsigned long long*>(cursor), first, loc_out, gid_out);
     }
     ACX_CUDA(cudaGetLastError());

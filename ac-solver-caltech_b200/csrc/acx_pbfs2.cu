@@ -234,6 +234,7 @@ struct Pb3Params {
     int64_t* ctl;
     int64_t* parent;
     uint8_t* action;
+    int64_t* round_log;           // commit: {first place, end place, first global id, new nodes} of the round, or NULL
 };
 
 static constexpr unsigned long long PB_IN_ROUND = 1ull << 62;  // keeps the orders of a round apart from real global ids
@@ -467,6 +468,12 @@ __global__ void __launch_bounds__(256) k_pbfs_commit3(const Pb3Params p) {
     if (p.ctl[CTL_STOP] != 0) return;
     const int64_t re = *p.round_end < p.node_cap ? *p.round_end : p.node_cap;
     const int64_t gid_base = p.ctl[CTL_GID_BASE];
+    if (p.round_log && blockIdx.x == 0 && threadIdx.x == 0) {  // where the round's nodes are: the next level is grouped from it
+        p.round_log[0] = *p.round_start;
+        p.round_log[1] = re;
+        p.round_log[2] = gid_base;
+        p.round_log[3] = p.ctl[CTL_NODES] - gid_base;
+    }
   for (int64_t place = *p.round_start + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; place < re; place += (int64_t)gridDim.x * blockDim.x) {
     const unsigned long long o = p.gid[place];
     if (o == ~0ull) continue;  // a hole: reserved, never claimed
@@ -593,13 +600,14 @@ extern "C" int64_t acx_pbfs_decide(const uint16_t* mask16, int32_t* excl_out, in
 
 extern "C" int acx_pbfs_commit3(const int64_t* round_start_dev, const int64_t* round_end_dev, int64_t max_new, int64_t node_cap,
                                 const int32_t* excl, const uint32_t* mask32, int64_t parent_base, const int64_t* ctl, int64_t* gid,
-                                int64_t* parent, uint8_t* action, acx_stream_t stream) {
+                                int64_t* parent, uint8_t* action, int64_t* round_log, acx_stream_t stream) {
     if (!round_start_dev || !round_end_dev || !excl || !mask32 || !ctl || !gid || !parent || !action || max_new < 1 || node_cap < 1)
         return acx_fail(ACX_ERR_ARG, "acx_pbfs_commit3: bad argument");
     Pb3Params p = {};
     p.round_start = round_start_dev; p.round_end = round_end_dev; p.node_cap = node_cap;
     p.excl = excl; p.mask32 = const_cast<unsigned*>(mask32); p.parent_base = parent_base;
     p.ctl = const_cast<int64_t*>(ctl); p.gid = reinterpret_cast<unsigned long long*>(gid); p.parent = parent; p.action = action;
+    p.round_log = round_log;
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -277,7 +277,9 @@ int acx_pbfs_commit(const uint64_t* recs, const int64_t* region_counts, int n_re
  *   acx_pbfs_decide   exclusive scan of popcount(mask16) -> excl_out (int32), then the decision of the round
  *                     (breadth_first.py:84-95 in the reference's order) into ctl.  temp == NULL returns the scratch size.
  *   acx_pbfs_commit3  the places [round_start, round_end) get global id ctl[3] + excl[p] + popcount(mask16[p] & bits below a),
- *                     parent and action from their winning order (p, a); max_new bounds round_end - round_start. */
+ *                     parent and action from their winning order (p, a); max_new bounds round_end - round_start.
+ *                     round_log (may be NULL): four words {round_start, round_end, first global id, new nodes} of the
+ *                     round, from which the driver finds the places that hold a window of the next level. */
 int acx_pbfs_expand2(const uint64_t* nodes, const uint8_t* action, const int64_t* loc, const int64_t* gids, int64_t ord_base,
                      int64_t f, int m, int cyclical, int world, int64_t region_cap, uint64_t* cursor,
                      uint8_t* const* dst_regions, const int64_t* ctl, acx_stream_t stream);
@@ -289,7 +291,7 @@ int64_t acx_pbfs_decide(const uint16_t* mask16, int32_t* excl_out, int64_t n_par
                         acx_stream_t stream);
 int acx_pbfs_commit3(const int64_t* round_start_dev, const int64_t* round_end_dev, int64_t max_new, int64_t node_cap,
                      const int32_t* excl, const uint32_t* mask32, int64_t parent_base, const int64_t* ctl, int64_t* gid,
-                     int64_t* parent, uint8_t* action, acx_stream_t stream);
+                     int64_t* parent, uint8_t* action, int64_t* round_log, acx_stream_t stream);
 
 /* Exclusive scan of popcount(mask[p]) over the parents of a round: excl_out[p] = new nodes discovered by the
  * parents before p (reference order), total_out[0] = new nodes of the round.  temp == NULL returns the scratch
