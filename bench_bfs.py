@@ -134,6 +134,9 @@ def bfs_leg(dev, budget=10 ** 9, chunk_per_rank=1 << 20, large=True, peak_gbs=65
     # record written and read once + one 8-byte table slot read, every new node written once with its slot, id, parent
     # and action
     alg = 32.0 * exp + (32 + 32 + 8) * cand + (32 + 8 + 8 + 8 + 1) * seen
+    # what bounds a hash-table probe is random memory operations, not bytes: one slot read per candidate and
+    # one claim per new node, against the rate tools/random_access.cu measures (profiles/r02_random_access_microbench.jsonl)
+    rand_ops, rand_peak = float(cand + seen), 36.4e9
     out = {
         "config": "BASELINE configs[3]: level-synchronous bfs from AK(3), max_relator_length=36, "
                   "cyclically_reduce_after_moves=False, max_nodes_to_explore=%d, visited set hash-partitioned over %d GPU(s)" % (budget, world),
@@ -145,7 +148,11 @@ def bfs_leg(dev, budget=10 ** 9, chunk_per_rank=1 << 20, large=True, peak_gbs=65
         "store_holes": prof["store_holes"], "phase_ms": prof["phase_ms"], "phase_ms_note": "max over ranks, from a separate run with a device sync per phase (%.1f ms in all)" % (1e3 * prof["wall_s"]),
         "roofline": {"bound": "hbm", "achieved": alg / dt / 1e9 / world, "peak": peak_gbs, "unit": "GB/s per GPU",
                      "frac": alg / dt / 1e9 / world / peak_gbs, "alg_bytes_per_node_expanded": alg / max(exp, 1),
-                     "nvlink_frac": best["sent_bytes"] / world / dt / 1e9 / 900.0},
+                     "nvlink_frac": best["sent_bytes"] / world / dt / 1e9 / 900.0,
+                     "random_ops": {"per_s_per_gpu": rand_ops / dt / world, "peak_per_s": rand_peak, "frac": rand_ops / dt / world / rand_peak,
+                                    "frac_in_probe": (rand_ops / world / (1e-3 * prof["phase_ms"]["probe"]) / rand_peak) if prof["phase_ms"] else None,
+                                    "ops": "slot read per candidate + claim per new node",
+                                    "peak_source": "tools/random_access.cu: random 8-byte loads over 34 GB on one B200"}},
         "parity": parity, "parity_cases": detail,
         "reference": "breadth_first.py: 660 nodes expanded/s on one core (SURVEY.md section 6)",
     }
