@@ -62,7 +62,7 @@ class PlaneShard2(PlaneShard):
         # acx_pbfs_probe3 appends a node the moment it claims a state: the round that the budget cuts may append up to
         # 12 children per parent beyond the budget, and so may the round behind it (its probe runs next to the decision
         # of the round that stops the search); a reserved place whose claim lost its race can stay a hole
-        cap = int(cap_local) + 24 * int(max_parents) + 3 * int(cap_local) // 100 + (1 << 18)  # holes: 1.4 % measured from AK(3)
+        cap = int(cap_local) + 24 * int(max_parents) + 5 * int(cap_local) // 100 + (1 << 18)  # holes: 1.4 - 2.2 % measured from AK(3)
         super().__init__(m, cyclical, cap, max_parents, device, transport)
 
     def seed(self, root):

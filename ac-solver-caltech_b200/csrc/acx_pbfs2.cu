@@ -322,8 +322,21 @@ __global__ void __launch_bounds__(NT, MINB) k_pbfs_probe3(const Pb3Params p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int64_t spare = -1;
     if (threadIdx.x == 0) s_pool[0] = s_pool[1] = 0;
-    for (int64_t base = (int64_t)blockIdx.x * NT; base < cnt; base += T) {  // block-uniform: the CTA meets at the barriers
-        const int64_t i = base + threadIdx.x;
+    // A large round is walked with a stride: iteration `it` of thread t takes record it * T + t (coalesced record loads).
+    // A small round -- fewer than 17 records per thread -- is walked in blocks instead: thread t takes the 17 CONSECUTIVE
+    // records [17 t, 17 t + 17), one per iteration, and the rest of the grid idles.  Equal candidates sit close to each other
+    // in a region (children of sibling parents, mostly a multiple of 32 records apart); handled by neighbouring threads in
+    // the same iteration they race for the empty slot and the loser's place is wasted unless the thread claims again
+    // later, which in a small round it never does (one record per thread: a fifth of the store became holes).  17 is odd:
+    // records 32 apart fall into different iterations.
+    constexpr int64_t RB = 17;
+    const int64_t per_thread = (cnt + T - 1) / T;
+    const bool blocked = per_thread < RB;
+    const int64_t gt = (int64_t)blockIdx.x * NT + threadIdx.x;
+    if ((int64_t)blockIdx.x * NT * (blocked ? RB : 1) >= cnt) return;  // block-uniform
+    const int64_t R = blocked ? RB : (cnt - (int64_t)blockIdx.x * NT + T - 1) / T;  // iterations of THIS CTA
+    for (int64_t it = 0; it < R; ++it) {  // block-uniform: the CTA meets at the barriers
+        const int64_t i = blocked ? gt * RB + it : it * T + gt;
         bool live = false, settled = true;
         PWords st;
         st.w[0] = st.w[1] = st.w[2] = st.w[3] = 0ull;
@@ -366,7 +379,7 @@ __global__ void __launch_bounds__(NT, MINB) k_pbfs_probe3(const Pb3Params p) {
                 s_pool[0] = pb + total;
                 s_pool[1] = left - total;
             } else {  // the pool runs dry: what it holds goes first, the rest comes from a new chunk
-                const int64_t iters_left = (cnt - base + T - 1) / T;  // this one included
+                const int64_t iters_left = R - it;  // this one included
                 const long long mult = iters_left - 1 > 8 ? 8 : (iters_left - 1 < 1 ? 1 : iters_left - 1);
                 const long long want = (long long)(total - left) + (mult - 1) * total;
                 const long long nb = (long long)atomicAdd(p.n_local, (unsigned long long)want);

@@ -157,7 +157,9 @@ def test_plane_bfs_device_driven_single_rank(cuda, oracle, golden_dir):
         rows = dataset_rows(golden_dir)
         rng = np.random.default_rng(33)
         cases = [(repad(AK2, 8), 4000, False, 64), (repad(AK2, 8), 4000, False, 1 << 16), (pad_row(*AK3, 36), 200000, False, 4096),
-                 (pad_row(*AK3, 36), 50000, True, 100000), (pad_row(*AK3, 36), 1500000, False, 1 << 18)]
+                 (pad_row(*AK3, 36), 50000, True, 100000), (pad_row(*AK3, 36), 1500000, False, 1 << 18),
+                 # levels of more than 64 rounds (grouped block by block from the round log), a chunk that is no power of two
+                 (pad_row(*AK3, 36), 60000, False, 64), (pad_row(*AK3, 36), 40000, True, 100)]
         for k in rng.choice(len(rows), size=10, replace=False):
             for budget, chunk in ((1, 4), (13, 4), (14, 4), (700, 64), (30000, 256), (30000, 4096)):
                 cases.append((rows[int(k)], budget, bool(rng.integers(0, 2)), chunk))
@@ -174,6 +176,83 @@ def test_plane_bfs_device_driven_single_rank(cuda, oracle, golden_dir):
             assert eng.n_nodes == stats["n_seen"] and eng.n_expanded == stats["n_expanded"], (budget, cyc, chunk)
             n_solved += int(ok)
         assert n_solved >= 1
+    finally:
+        if created:
+            dist.destroy_process_group()
+
+
+def test_window_partition_blocks_and_holes(cuda):
+    """acx_bfs_window_partition groups local nodes by round; ids outside [lo, lo + n_windows * chunk) -- another block of
+    the level's windows, or -1 = a hole of the node store -- are left out (numpy restatement)"""
+    import torch
+
+    from acx import _lib
+    from acx.batch import _ptr
+
+    L = _lib.lib()
+    rng = np.random.default_rng(5)
+    stream = torch.cuda.current_stream(cuda).cuda_stream
+    for n, chunk, lo, nwin in ((1, 4, 0, 1), (5000, 64, 100, 7), (300000, 1000, 12345, 40), (300000, 1 << 12, 4096, 64), (70000, 3, 10, 2000)):
+        g = rng.integers(lo - 3 * chunk, lo + (nwin + 5) * chunk, size=n)
+        g[rng.random(n) < 0.05] = -1
+        first = 17
+        gid = torch.from_numpy(g).to(cuda)
+        counts = torch.zeros(nwin, dtype=torch.int64, device=cuda)
+        _lib.check(L.acx_bfs_window_partition(_ptr(gid), n, lo, chunk, nwin, _ptr(counts), 0, 0, first, 0, 0, 0, stream), "count")
+        keep = (g >= lo) & (g < lo + nwin * chunk)
+        w = (g[keep] - lo) // chunk
+        want = np.bincount(w, minlength=nwin)
+        assert counts.cpu().numpy().tolist() == want.tolist(), (n, chunk)
+        ends = torch.cumsum(counts, 0)
+        offsets = (ends - counts).contiguous()
+        cursor = torch.zeros(nwin, dtype=torch.int64, device=cuda)
+        loc = torch.full((n,), -7, dtype=torch.int64, device=cuda)
+        out = torch.full((n,), -7, dtype=torch.int64, device=cuda)
+        _lib.check(L.acx_bfs_window_partition(_ptr(gid), n, lo, chunk, nwin, _ptr(counts), _ptr(offsets), _ptr(cursor), first,
+                                              _ptr(loc), _ptr(out), 1, stream), "scatter")
+        loc, out, e = loc.cpu().numpy(), out.cpu().numpy(), ends.cpu().numpy()
+        total = int(keep.sum())
+        assert (loc[total:] == -7).all() and (out[total:] == -7).all()
+        assert (g[loc[:total] - first] == out[:total]).all()                  # every entry names a node and carries its id
+        assert sorted(loc[:total].tolist()) == (np.flatnonzero(keep) + first).tolist()  # each kept node exactly once
+        b = 0
+        for k in range(nwin):                                                   # grouped by window, any order inside
+            seg = out[b:e[k]]
+            assert ((seg - lo) // chunk == k).all()
+            b = e[k]
+
+
+def test_plane_bfs_store_invariants(cuda, oracle):
+    """after a search that ran into its budget: every place of the node store below the last round is a node with a
+    global id, or a hole (gid -1, zero node) that no table slot names; ids 0 .. n-1 appear exactly once"""
+    import torch
+    import torch.distributed as dist
+
+    from acx.pbfs import PlaneBFS, make_plane_shard
+    from helpers import AK3, pad_row
+
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", str(29700 + os.getpid() % 200))
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=cuda)
+    try:
+        row, budget = pad_row(*AK3, 36), 300000
+        shard = make_plane_shard(row, False, budget + 64, 1 << 12, str(cuda))
+        eng = PlaneBFS(row, budget, shard, chunk=1 << 12)
+        ok, _ = eng.run()
+        assert not ok
+        n_local = int(shard.n_local_dev.item())
+        gid = shard.gid[:n_local].cpu().numpy()
+        nodes = shard.nodes[:n_local].cpu().numpy()
+        committed = (gid >= 0) & (gid < (1 << 62))
+        holes = gid == -1
+        tail = ~committed & ~holes                      # the round the budget cut (and the one behind it): orders, not ids
+        assert (nodes[holes] == 0).all() and (nodes[committed, 0] != 0).all()
+        ids = np.sort(gid[committed])
+        assert (ids == np.arange(len(ids))).all()        # the discovery ranks of the reference, each exactly once
+        assert len(ids) <= eng.n_nodes <= len(ids) + int(tail.sum())
+        assert holes.sum() <= 0.1 * n_local + 4096
     finally:
         if created:
             dist.destroy_process_group()
