@@ -226,7 +226,10 @@ class VecACEnv:
         The returned arrays are views of pinned staging buffers that the next step overwrites.  Raises
         AssertionError where the reference's ACMove would (invalid row / emptied relator, utils.py:264-266)."""
         a = np.asarray(actions)
-        self._h_act.numpy()[:] = a  # dtype conversion into pinned memory
+        try:  # dtype conversion into pinned memory: torch's vectorised cast (0.1 ms per 2^20 int64 actions, numpy's takes 0.45)
+            self._h_act.copy_(torch.from_numpy(a))
+        except (TypeError, ValueError, RuntimeError):  # a dtype or layout torch does not take
+            self._h_act.numpy()[:] = a
         self._d_act.copy_(self._h_act, non_blocking=True)
         b = batch.env_step(self.buf, self._d_act, next_idx=self.next_state_index, clip=self.clip)
         self._h_obs.copy_(b.state, non_blocking=True)
