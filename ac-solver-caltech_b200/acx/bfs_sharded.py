@@ -143,8 +143,11 @@ class GpuShard:
             self.sends = [torch.empty((G * self.rcap, self.rec), dtype=torch.uint8, device=self.dev) for _ in range(self.n_bufs)]
             self.dst = [[b.data_ptr() + g * self.rcap * self.rec for g in range(G)] for b in self.sends]
         self._group = group
-        # frontier index buffers of a level (local index, global id), allocated once: a level can be most of the shard
-        self._part = (torch.empty((self.cap,), dtype=torch.int64, device=self.dev), torch.empty((self.cap,), dtype=torch.int64, device=self.dev))
+        self._part = self._alloc_part()
+
+    def _alloc_part(self):
+        """frontier index buffers of a level (local index, global id), allocated once: a level can be most of the shard"""
+        return (torch.empty((self.cap,), dtype=torch.int64, device=self.dev), torch.empty((self.cap,), dtype=torch.int64, device=self.dev))
 
     def _fusable(self, world):
         return self.m == 36 and world <= 32

@@ -28,6 +28,7 @@ from .bfs_sharded import PlaneShard, ShardedBFS
 
 SENT = 1 << 62
 STOP_SOLVED, STOP_ERROR, STOP_BUDGET = 1, 2, 3
+WB = 64  # rounds (windows of a level) grouped per pass over the level's nodes
 
 
 _count_groups = {}
@@ -64,6 +65,12 @@ class PlaneShard2(PlaneShard):
         # of the round that stops the search); a reserved place whose claim lost its race can stay a hole
         cap = int(cap_local) + 24 * int(max_parents) + 5 * int(cap_local) // 100 + (1 << 18)  # holes: 1.4 - 2.2 % measured from AK(3)
         super().__init__(m, cyclical, cap, max_parents, device, transport)
+
+    def _alloc_part(self):
+        """PlaneBFS groups a level WB rounds at a time: the index buffers hold one block of rounds, not the level
+        (2 x 8 bytes per node of the shard otherwise: 17 GB at 1e9 nodes)"""
+        n = min(self.cap, WB * self.fmax + 4096)
+        return (torch.empty((n,), dtype=torch.int64, device=self.dev), torch.empty((n,), dtype=torch.int64, device=self.dev))
 
     def seed(self, root):
         super().seed(root)
@@ -151,7 +158,6 @@ class PlaneBFS(ShardedBFS):
         # the host runs at most `ahead` rounds in front of the device: it waits for the event of round k - ahead, looks
         # at that round's copy of the stop code (pinned memory) and stops enqueueing when the search has ended
         ahead = 4
-        WB = 64  # windows grouped per pass over the level's nodes
         LOGCAP = 4096  # rounds of one level whose place ranges are logged (a longer level is grouped from all its nodes)
         round_log = torch.zeros((LOGCAP, 4), dtype=torch.int64, device=dev)
         prev_log, level_k0 = None, 0  # the log of the previous level (numpy [rounds, 4]), first round of this level
