@@ -46,6 +46,21 @@ def _count_group(group):
     return _count_groups[key]
 
 
+def block_places(round_log, blo, bhi, first, n_local):
+    """The places [a, b) of the local node store that can hold nodes with a global id in [blo, bhi).  round_log: one row
+    {first place, end place, first global id, new nodes} per round of the level that discovered those nodes (numpy
+    [rounds, 4], written by acx_pbfs_commit3), or None = unknown: every place of that level, [first, n_local).  The rounds
+    of a level append their nodes to consecutive places and give them consecutive global ids, so the answer is the span
+    of the rounds whose id range meets [blo, bhi); rounds that appended nothing on this rank do not count."""
+    if round_log is None:
+        return first, n_local
+    log = np.asarray(round_log, dtype=np.int64).reshape(-1, 4)
+    hit = (log[:, 2] < bhi) & (log[:, 2] + log[:, 3] > blo) & (log[:, 1] > log[:, 0])
+    if not hit.any():
+        return first, first
+    return max(first, int(log[hit, 0].min())), min(n_local, int(log[hit, 1].max()))
+
+
 class PlaneShard2(PlaneShard):
     """PlaneShard whose regions hold runs padded to whole 128-byte lines (four records), with a node store that
     acx_pbfs_probe3 appends to (head room for the rounds around a stop and for holes).  Three exchange buffers: the
@@ -231,15 +246,7 @@ class PlaneBFS(ShardedBFS):
                     loc = torch.arange(first, n_local, dtype=torch.int64, device=dev, out=s._part[0][: n_local - first])
                     gids, cuts = gl, [0, n_local - first]
                 else:
-                    a, b = first, n_local
-                    if prev_log is not None:
-                        # the rounds of the previous level appended their nodes to contiguous places, with contiguous
-                        # global ids: only the places of the rounds that reach into this block of windows are grouped
-                        hit = (prev_log[:, 2] < bhi) & (prev_log[:, 2] + prev_log[:, 3] > blo) & (prev_log[:, 1] > prev_log[:, 0])
-                        if hit.any():
-                            a, b = max(first, int(prev_log[hit, 0].min())), min(n_local, int(prev_log[hit, 1].max()))
-                        else:
-                            a = b = first
+                    a, b = block_places(prev_log, blo, bhi, first, n_local)
                     loc, gids, cuts = s.window_partition(s.gid[a:b], a, blo, C_max, nb)
                 self._tick("level_sort")
                 offs = list(range(blo, bhi, C_max))
